@@ -1,0 +1,155 @@
+/* rt_b200.h — C ABI of librt_b200.so: the per-pixel path-tracing loop of the reference's
+ * shaders/fragment.glsl as hand-written sm_100a CUDA, behind the call sites where the reference
+ * talks to OpenGL.  Plain C types only; no exceptions cross this boundary.
+ *
+ * Every entry point replaces a group of PyOpenGL calls in the reference (paths under /root/reference):
+ *
+ *   rt_create / rt_destroy      GL context + shader program        main.py:115-147, main.py:444-445
+ *   rt_scene_upload             3x glBufferData + glBindBufferBase  scene.py:223-236
+ *   rt_scene_free               glDeleteBuffers                     scene.py:423-424
+ *   rt_set_params               glUniform* block                    main.py:175-202, 332-335, 358
+ *   rt_target_create / _clear   RGBA32F ping-pong textures + FBOs   screen.py:37-59, main.py:264-267
+ *   rt_render_pass              bind prev, frameNumber/tileX/tileY,
+ *                               bind next FBO, glDrawArrays         main.py:376-394, 401
+ *   rt_render_frames            the tile/frame sequencing loop      main.py:409-430
+ *   rt_read_rgba8               glBlitFramebuffer + glReadPixels    main.py:397-399, 434
+ *   rt_read_accum_f32           (texture read-back of accum_tex)    screen.py:42
+ *
+ * Conventions: functions return RT_OK (0) or a negative rt_status; rt_last_error(ctx) gives the text
+ * (the Python binding raises RuntimeError with it, standing in for PyOpenGL's GLError).  The caller owns
+ * every host buffer; the library copies what it needs and owns all device memory.  A context is bound
+ * to one CUDA device and is used from one host thread at a time (the reference's GL context is
+ * thread-affine too, main.py:289).  Multi-GPU runs use one context per process per GPU.
+ *
+ * Framebuffer orientation is OpenGL's: row 0 is the bottom row (gl_FragCoord.y = 0.5).
+ */
+#ifndef RT_B200_H
+#define RT_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct rt_ctx rt_ctx;
+
+typedef enum rt_status {
+    RT_OK = 0,
+    RT_ERR_INVALID = -1,   /* bad argument or malformed scene buffers */
+    RT_ERR_CUDA = -2,      /* a CUDA runtime call failed; see rt_last_error */
+    RT_ERR_STATE = -3,     /* call out of order (no scene / no target / no params) */
+    RT_ERR_NOMEM = -4
+} rt_status;
+
+/* The shader's uniform block, fragment.glsl:7-38, same names (bool lambertian as int32).
+ * Vectors are 3 floats.  total_frames, fov and trisCount are carried but unused, as in the shader. */
+typedef struct rt_params {
+    int32_t tileX, tileY, tileSizeX, tileSizeY, numTilesX, numTilesY;
+    int32_t total_frames;
+    int32_t lambertian;
+    float skyBrightness;
+    float fov, xStep, yStep, dirStartX, dirStartY;
+    float camPos[3], camRight[3], camUp[3], camForward[3];
+    int32_t nBounces, rays_per_pixel;
+    float jitterAmount;
+    int32_t frameNumber;
+    int32_t trisCount, boundingBoxCount;
+} rt_params;
+
+/* Work counters, reference-equivalent: what the shader would have executed for the same pass. */
+enum {
+    RT_CNT_RAYS = 0,          /* raycast() calls (fragment.glsl:246), incl. the re-traced primary of each sample */
+    RT_CNT_RAYS_TRACED = 1,   /* traversals actually executed by this library (primary hit reused across samples) */
+    RT_CNT_INTERNAL = 2,      /* internal nodes expanded (both children slab-tested, :281-304) */
+    RT_CNT_LEAVES = 3,        /* leaves entered (:266-279) */
+    RT_CNT_TRI_TESTS = 4,     /* rayTriangleIntersects calls (:274) */
+    RT_CNT_HITS = 5,          /* rays whose closest hit exists */
+    RT_CNT_POPS = 6,          /* stack pops incl. culled ones (:256-262) */
+    RT_CNT_PATHS = 7,         /* raytrace() calls = pixels x rays_per_pixel in the tile */
+    RT_CNT_COUNT = 8
+};
+
+/* Kernel variants (rt_set_variant); all produce identical results. */
+enum {
+    RT_VARIANT_AUTO = 0,
+    RT_VARIANT_PIXEL = 1,       /* one thread per pixel, whole pixel-frame in one kernel */
+    RT_VARIANT_PERSISTENT = 2,  /* persistent warps fetching pixels with warp-aggregated atomics */
+    RT_VARIANT_WAVEFRONT = 3    /* generate / extend / shade kernels over compacted ray queues */
+};
+
+/* flags for rt_render_pass_ex */
+enum {
+    RT_PASS_DEFAULT = 0,
+    RT_PASS_COUNTERS = 1,      /* accumulate the work counters (slower kernel instantiation) */
+    RT_PASS_PRIMARY_IDS = 2,   /* record the primary-hit triangle id image (-1 = miss) */
+    RT_PASS_SKIP_MASKED = 4    /* pixels outside the tile are left untouched instead of copied from
+                                  the previous target (multi-GPU band sharding: each GPU owns its rows) */
+};
+
+int rt_create(rt_ctx** out, int device);
+void rt_destroy(rt_ctx* ctx);
+const char* rt_last_error(rt_ctx* ctx);
+const char* rt_version(void);
+
+/* Run on a caller-provided CUDA stream (cudaStream_t as void*; e.g. torch's current stream) so the
+ * caller's events bracket the kernels.  NULL restores the context's own stream. */
+int rt_set_stream(rt_ctx* ctx, void* cuda_stream);
+int rt_sync(rt_ctx* ctx);
+
+/* tris: n_tris x 144 B, boxes: n_boxes x 48 B, indices: n_indices x u32 (layouts: scene.py:45-70).
+ * Validates every child / offset / index, copies, and builds the device layout. */
+int rt_scene_upload(rt_ctx* ctx, const void* tris, uint32_t n_tris, const void* boxes, uint32_t n_boxes,
+                    const uint32_t* indices, uint32_t n_indices);
+int rt_scene_free(rt_ctx* ctx);
+
+int rt_set_params(rt_ctx* ctx, const rt_params* params);
+int rt_set_variant(rt_ctx* ctx, int variant);
+
+/* Two width x height RGBA32F accumulation targets, cleared to 0; accum_index = 0, like screen.py:61-66. */
+int rt_target_create(rt_ctx* ctx, int width, int height);
+int rt_target_clear(rt_ctx* ctx);
+int rt_target_free(rt_ctx* ctx);
+
+/* One draw: reads target[accum_index], writes target[1 - accum_index], then flips accum_index
+ * (main.py:376-401).  frameNumber / tileX / tileY override the values given to rt_set_params. */
+int rt_render_pass(rt_ctx* ctx, int frameNumber, int tileX, int tileY);
+int rt_render_pass_ex(rt_ctx* ctx, int frameNumber, int tileX, int tileY, int flags);
+
+/* n_frames whole frames starting at first_frame, every tile of each frame in the reference's order
+ * (tileX fastest, main.py:409-418), frameNumber advancing by frame_stride (1 = the reference's loop;
+ * G = this GPU's share of a frame-sharded progressive run, in which case the targets hold the running
+ * SUM of this GPU's frames instead of the running mean — see rt_render_frames_sum). */
+int rt_render_frames(rt_ctx* ctx, int first_frame, int n_frames);
+int rt_render_frames_sum(rt_ctx* ctx, int first_frame, int n_frames, int frame_stride);
+
+/* Read-backs of the current accumulation target (the one the last pass wrote). */
+int rt_read_accum_f32(rt_ctx* ctx, float* dst_rgba);        /* width*height*4 floats */
+int rt_read_rgba8(rt_ctx* ctx, uint8_t* dst_rgba);          /* round(clamp(x,0,1)*255), main.py:434 */
+int rt_read_primary_ids(rt_ctx* ctx, int32_t* dst);         /* width*height, needs RT_PASS_PRIMARY_IDS */
+int rt_read_counters(rt_ctx* ctx, uint64_t* dst, int n);    /* RT_CNT_* since rt_reset_counters */
+int rt_reset_counters(rt_ctx* ctx);
+
+/* Device pointers for zero-copy hand-off (torch via __cuda_array_interface__): which = 0/1 selects a
+ * target, -1 the current one.  rt_accum_index returns which target is current. */
+void* rt_accum_device_ptr(rt_ctx* ctx, int which);
+int rt_accum_index(rt_ctx* ctx);
+int rt_set_accum_index(rt_ctx* ctx, int index);
+
+/* Band sharding helpers (multi-GPU tile mode): copy the rows owned by tile row `tileY` (rows y with
+ * (y / tileSizeY) % numTilesY == tileY) of the current target to/from a dense device buffer. */
+int rt_band_rows(rt_ctx* ctx, int tileY);                                   /* how many rows */
+int rt_band_gather(rt_ctx* ctx, int tileY, void* dense_dev);                /* target -> dense */
+int rt_band_scatter(rt_ctx* ctx, int tileY, const void* dense_dev);         /* dense -> target */
+/* sum target -> mean RGBA32F in place: target = target * (1 / n_frames) is NOT what the reference
+ * does; it divides.  Used after the frame-sharded reduce. */
+int rt_finish_sum(rt_ctx* ctx, int total_frames);
+
+/* Stream-ordered timing on the context's stream (for callers without a CUDA event API). */
+int rt_timer_start(rt_ctx* ctx);
+int rt_timer_stop(rt_ctx* ctx, float* milliseconds);   /* synchronises */
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* RT_B200_H */

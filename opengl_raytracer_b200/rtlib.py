@@ -1,0 +1,281 @@
+"""ctypes binding of ``librt_b200.so`` (C ABI: ``include/rt_b200.h``).
+
+This is the drop-in boundary: where the reference's host code calls PyOpenGL (``glBufferData``,
+``glUniform*``, ``glDrawArrays``, ``glReadPixels`` — /root/reference/scene.py:223-236,
+main.py:175-202,376-399,434) this module calls the device library.  Errors surface as ``RuntimeError``
+carrying ``rt_last_error`` — the counterpart of PyOpenGL raising ``GLError``.  There is no CPU path:
+if the CUDA library is missing or no GPU is present the calls raise.
+
+Like a GL context, a :class:`Context` can be made *current* so that ``Scene.send()`` and ``Screen``
+find it without being handed one (the reference relies on the thread's current GL context).
+"""
+from __future__ import annotations
+
+import ctypes
+import os
+
+import numpy as np
+
+from .configs import RenderParams
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "csrc", "librt_b200.so")
+
+c_f3 = ctypes.c_float * 3
+
+
+class RtParams(ctypes.Structure):
+    """``struct rt_params`` — the shader's uniform block (fragment.glsl:7-38)."""
+    _fields_ = [
+        ("tileX", ctypes.c_int32), ("tileY", ctypes.c_int32),
+        ("tileSizeX", ctypes.c_int32), ("tileSizeY", ctypes.c_int32),
+        ("numTilesX", ctypes.c_int32), ("numTilesY", ctypes.c_int32),
+        ("total_frames", ctypes.c_int32), ("lambertian", ctypes.c_int32),
+        ("skyBrightness", ctypes.c_float), ("fov", ctypes.c_float),
+        ("xStep", ctypes.c_float), ("yStep", ctypes.c_float),
+        ("dirStartX", ctypes.c_float), ("dirStartY", ctypes.c_float),
+        ("camPos", c_f3), ("camRight", c_f3), ("camUp", c_f3), ("camForward", c_f3),
+        ("nBounces", ctypes.c_int32), ("rays_per_pixel", ctypes.c_int32),
+        ("jitterAmount", ctypes.c_float), ("frameNumber", ctypes.c_int32),
+        ("trisCount", ctypes.c_int32), ("boundingBoxCount", ctypes.c_int32),
+    ]
+
+    @classmethod
+    def from_render_params(cls, p: RenderParams) -> "RtParams":
+        out = cls()
+        for name, _ in cls._fields_:
+            value = getattr(p, name)
+            if name in ("camPos", "camRight", "camUp", "camForward"):
+                setattr(out, name, c_f3(*[float(x) for x in value]))
+            else:
+                setattr(out, name, value)
+        return out
+
+
+COUNTER_NAMES = ("rays", "rays_traced", "internal", "leaves", "tri_tests", "hits", "pops", "paths")
+VARIANTS = {"auto": 0, "pixel": 1, "persistent": 2, "wavefront": 3}
+PASS_COUNTERS, PASS_PRIMARY_IDS, PASS_SKIP_MASKED = 1, 2, 4
+
+_lib = None
+
+
+def load_library(path: str | None = None):
+    """dlopen ``librt_b200.so`` and declare every prototype of ``include/rt_b200.h``."""
+    global _lib
+    if _lib is not None and path is None:
+        return _lib
+    path = path or LIB_PATH
+    if not os.path.isfile(path):
+        raise RuntimeError(f"{path} not built — run `python -c 'import __graft_entry__ as g; g.build()'` "
+                           "(there is no CPU fallback for the render path)")
+    lib = ctypes.CDLL(path)
+    vp, i, u32, P = ctypes.c_void_p, ctypes.c_int, ctypes.c_uint32, ctypes.POINTER
+    protos = {
+        "rt_create": (i, [P(vp), i]),
+        "rt_destroy": (None, [vp]),
+        "rt_last_error": (ctypes.c_char_p, [vp]),
+        "rt_version": (ctypes.c_char_p, []),
+        "rt_set_stream": (i, [vp, vp]),
+        "rt_sync": (i, [vp]),
+        "rt_scene_upload": (i, [vp, vp, u32, vp, u32, vp, u32]),
+        "rt_scene_free": (i, [vp]),
+        "rt_set_params": (i, [vp, P(RtParams)]),
+        "rt_set_variant": (i, [vp, i]),
+        "rt_target_create": (i, [vp, i, i]),
+        "rt_target_clear": (i, [vp]),
+        "rt_target_free": (i, [vp]),
+        "rt_render_pass": (i, [vp, i, i, i]),
+        "rt_render_pass_ex": (i, [vp, i, i, i, i]),
+        "rt_render_frames": (i, [vp, i, i]),
+        "rt_render_frames_sum": (i, [vp, i, i, i]),
+        "rt_read_accum_f32": (i, [vp, vp]),
+        "rt_read_rgba8": (i, [vp, vp]),
+        "rt_read_primary_ids": (i, [vp, vp]),
+        "rt_read_counters": (i, [vp, vp, i]),
+        "rt_reset_counters": (i, [vp]),
+        "rt_accum_device_ptr": (vp, [vp, i]),
+        "rt_accum_index": (i, [vp]),
+        "rt_set_accum_index": (i, [vp, i]),
+        "rt_band_rows": (i, [vp, i]),
+        "rt_band_gather": (i, [vp, i, vp]),
+        "rt_band_scatter": (i, [vp, i, vp]),
+        "rt_finish_sum": (i, [vp, i]),
+        "rt_timer_start": (i, [vp]),
+        "rt_timer_stop": (i, [vp, P(ctypes.c_float)]),
+    }
+    for name, (res, args) in protos.items():
+        fn = getattr(lib, name)
+        fn.restype, fn.argtypes = res, args
+    if path == LIB_PATH:
+        _lib = lib
+    return lib
+
+
+_current = None
+
+
+def current_context() -> "Context":
+    if _current is None:
+        raise RuntimeError("no current rt context — create Context(...) first (the reference needs a GL context here)")
+    return _current
+
+
+class Context:
+    """One device context = the reference's GL context + compiled shader program (main.py:115-147)."""
+
+    def __init__(self, device: int = 0, make_current: bool = True, lib_path: str | None = None):
+        self.lib = load_library(lib_path)
+        handle = ctypes.c_void_p()
+        rc = self.lib.rt_create(ctypes.byref(handle), int(device))
+        if rc != 0 or not handle:
+            raise RuntimeError(f"rt_create(device={device}) failed with {rc}: is a CUDA GPU present?")
+        self.handle = handle
+        self.device = device
+        self.width = self.height = 0
+        if make_current:
+            self.make_current()
+
+    # -- plumbing
+    def make_current(self):
+        global _current
+        _current = self
+
+    def _check(self, rc):
+        if rc != 0:
+            msg = self.lib.rt_last_error(self.handle)
+            raise RuntimeError(f"librt_b200 error {rc}: {msg.decode() if msg else '?'}")
+
+    def close(self):
+        global _current
+        if getattr(self, "handle", None):
+            self.lib.rt_destroy(self.handle)
+            self.handle = None
+            if _current is self:
+                _current = None
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *exc):
+        self.close()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    # -- scene (scene.py:223-236, 423-424)
+    def scene_upload(self, tris: np.ndarray, boxes: np.ndarray, indices: np.ndarray):
+        tris = np.ascontiguousarray(tris)
+        boxes = np.ascontiguousarray(boxes)
+        indices = np.ascontiguousarray(indices, dtype=np.uint32)
+        if tris.dtype.itemsize != 144 and tris.dtype != np.uint8:
+            raise ValueError("tris records must be 144 bytes")
+        n_tris = tris.nbytes // 144
+        n_boxes = boxes.nbytes // 48
+        self._check(self.lib.rt_scene_upload(self.handle, tris.ctypes.data, n_tris, boxes.ctypes.data, n_boxes,
+                                             indices.ctypes.data, indices.size))
+        self.n_tris, self.n_boxes = n_tris, n_boxes
+
+    def scene_free(self):
+        self._check(self.lib.rt_scene_free(self.handle))
+
+    # -- uniforms (main.py:175-202)
+    def set_params(self, params):
+        if isinstance(params, RenderParams):
+            params = RtParams.from_render_params(params)
+        self._params = params
+        self._check(self.lib.rt_set_params(self.handle, ctypes.byref(params)))
+
+    def set_variant(self, variant):
+        self._check(self.lib.rt_set_variant(self.handle, VARIANTS.get(variant, variant)))
+
+    def set_stream(self, cuda_stream: int | None):
+        self._check(self.lib.rt_set_stream(self.handle, ctypes.c_void_p(cuda_stream or 0)))
+
+    def sync(self):
+        self._check(self.lib.rt_sync(self.handle))
+
+    # -- targets (screen.py:37-59)
+    def target_create(self, width: int, height: int):
+        self._check(self.lib.rt_target_create(self.handle, width, height))
+        self.width, self.height = width, height
+
+    def target_clear(self):
+        self._check(self.lib.rt_target_clear(self.handle))
+
+    def target_free(self):
+        self._check(self.lib.rt_target_free(self.handle))
+        self.width = self.height = 0
+
+    # -- draw (main.py:376-394)
+    def render_pass(self, frameNumber: int, tileX: int = 0, tileY: int = 0, flags: int = 0):
+        self._check(self.lib.rt_render_pass_ex(self.handle, frameNumber, tileX, tileY, flags))
+
+    def render_frames(self, first_frame: int, n_frames: int):
+        self._check(self.lib.rt_render_frames(self.handle, first_frame, n_frames))
+
+    def render_frames_sum(self, first_frame: int, n_frames: int, frame_stride: int = 1):
+        self._check(self.lib.rt_render_frames_sum(self.handle, first_frame, n_frames, frame_stride))
+
+    def finish_sum(self, total_frames: int):
+        self._check(self.lib.rt_finish_sum(self.handle, total_frames))
+
+    # -- read-backs (main.py:397-399, 434)
+    def read_accum_f32(self, out: np.ndarray | None = None) -> np.ndarray:
+        if out is None:
+            out = np.empty((self.height, self.width, 4), dtype=np.float32)
+        self._check(self.lib.rt_read_accum_f32(self.handle, out.ctypes.data))
+        return out
+
+    def read_rgba8(self, out: np.ndarray | None = None) -> np.ndarray:
+        if out is None:
+            out = np.empty((self.height, self.width, 4), dtype=np.uint8)
+        self._check(self.lib.rt_read_rgba8(self.handle, out.ctypes.data))
+        return out
+
+    def read_primary_ids(self) -> np.ndarray:
+        out = np.empty((self.height, self.width), dtype=np.int32)
+        self._check(self.lib.rt_read_primary_ids(self.handle, out.ctypes.data))
+        return out
+
+    def read_counters(self) -> dict:
+        buf = np.zeros(len(COUNTER_NAMES), dtype=np.uint64)
+        self._check(self.lib.rt_read_counters(self.handle, buf.ctypes.data, buf.size))
+        return {k: int(v) for k, v in zip(COUNTER_NAMES, buf)}
+
+    def reset_counters(self):
+        self._check(self.lib.rt_reset_counters(self.handle))
+
+    # -- zero-copy hand-off / sharding helpers
+    def accum_device_ptr(self, which: int = -1) -> int:
+        return int(self.lib.rt_accum_device_ptr(self.handle, which) or 0)
+
+    @property
+    def accum_index(self) -> int:
+        return self.lib.rt_accum_index(self.handle)
+
+    @accum_index.setter
+    def accum_index(self, index: int):
+        self._check(self.lib.rt_set_accum_index(self.handle, index))
+
+    def band_rows(self, tileY: int) -> int:
+        rows = self.lib.rt_band_rows(self.handle, tileY)
+        if rows < 0:
+            self._check(rows)
+        return rows
+
+    def band_gather(self, tileY: int, dense_dev_ptr: int):
+        self._check(self.lib.rt_band_gather(self.handle, tileY, ctypes.c_void_p(dense_dev_ptr)))
+
+    def band_scatter(self, tileY: int, dense_dev_ptr: int):
+        self._check(self.lib.rt_band_scatter(self.handle, tileY, ctypes.c_void_p(dense_dev_ptr)))
+
+    def timer_start(self):
+        self._check(self.lib.rt_timer_start(self.handle))
+
+    def timer_stop(self) -> float:
+        ms = ctypes.c_float()
+        self._check(self.lib.rt_timer_stop(self.handle, ctypes.byref(ms)))
+        return ms.value
