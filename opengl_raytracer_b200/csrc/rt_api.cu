@@ -1,0 +1,596 @@
+// rt_api.cu — host side of librt_b200.so: the C ABI declared in include/rt_b200.h.
+//
+// Replaces the reference's PyOpenGL call sites (see the table at the top of rt_b200.h).  A context owns
+// one CUDA device's state: the re-laid-out scene, the uniform block, two RGBA32F accumulation targets
+// (ping-pong, screen.py:37-47) and a stream.  All device work is stream-ordered; read-backs synchronise.
+#include <cuda_runtime.h>
+
+#include <algorithm>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "../../include/rt_b200.h"
+#include "rt_types.h"
+
+// launchers (rt_kernels.cu)
+size_t rtPixelKernelSmem(int stackDepth);
+cudaError_t rtLaunchPixel(const PassParams& P, bool count, bool ids, cudaStream_t stream);
+cudaError_t rtLaunchPersistent(const PassParams& P, bool count, bool ids, int sms, cudaStream_t stream);
+cudaError_t rtLaunchToRgba8(const float4* src, uchar4* dst, size_t n, cudaStream_t stream);
+cudaError_t rtLaunchBandCopy(float4* target, float4* dense, int width, int rows, int tileSizeY, int numTilesY,
+                             int tile, int toDense, cudaStream_t stream);
+cudaError_t rtLaunchFinishSum(float4* target, size_t n, float frames, cudaStream_t stream);
+
+struct rt_ctx {
+    int device = 0;
+    int smCount = 148;
+    cudaStream_t ownStream = nullptr, stream = nullptr;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    std::string err;
+    // scene
+    NodeRec* dNodes = nullptr;
+    TriRec* dTris = nullptr;
+    ShadeRec* dShade = nullptr;
+    uint32_t* dTriId = nullptr;
+    uint2* dBig = nullptr;
+    DeviceScene scene{};
+    bool haveScene = false;
+    // uniforms
+    rt_params params{};
+    bool haveParams = false;
+    int variant = RT_VARIANT_AUTO;
+    // targets
+    int width = 0, height = 0;
+    float4* target[2] = {nullptr, nullptr};
+    int accumIndex = 0;
+    int32_t* dIds = nullptr;
+    uchar4* dRgba8 = nullptr;
+    unsigned long long* dCounters = nullptr;
+    unsigned int* dWork = nullptr;
+};
+
+namespace {
+
+int fail(rt_ctx* c, int code, const char* fmt, ...) {
+    char buf[512];
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(buf, sizeof buf, fmt, ap);
+    va_end(ap);
+    if (c) c->err = buf;
+    return code;
+}
+
+#define RT_CUDA(c, call)                                                                                  \
+    do {                                                                                                  \
+        cudaError_t e_ = (call);                                                                          \
+        if (e_ != cudaSuccess) return fail((c), RT_ERR_CUDA, "%s: %s", #call, cudaGetErrorString(e_));   \
+    } while (0)
+
+struct Bind {   // make the context's device current for the duration of a call
+    int prev = -1;
+    explicit Bind(rt_ctx* c) {
+        cudaGetDevice(&prev);
+        if (prev != c->device) cudaSetDevice(c->device);
+        else prev = -1;
+    }
+    ~Bind() {
+        if (prev >= 0) cudaSetDevice(prev);
+    }
+};
+
+// std430 records as the reference uploads them (scene.py:45-70).
+struct HostTri {
+    float v0p[3], p0, v0n[3], p1, v1p[3], p2, v1n[3], p3, v2p[3], p4, v2n[3], p5;
+    float color[3], p6, emc[3], p7, surface[2], p8[2];
+};
+struct HostBox {
+    uint32_t numTriangles, triangleOffset;
+    int32_t childA, childB;
+    float posMin[3], p0, posMax[3], p1;
+};
+static_assert(sizeof(HostTri) == 144 && sizeof(HostBox) == 48, "std430 layout");
+
+void freeScene(rt_ctx* c) {
+    cudaFree(c->dNodes); cudaFree(c->dTris); cudaFree(c->dShade); cudaFree(c->dTriId); cudaFree(c->dBig);
+    c->dNodes = nullptr; c->dTris = nullptr; c->dShade = nullptr; c->dTriId = nullptr; c->dBig = nullptr;
+    c->haveScene = false;
+    c->scene = DeviceScene{};
+}
+
+void freeTargets(rt_ctx* c) {
+    cudaFree(c->target[0]); cudaFree(c->target[1]); cudaFree(c->dIds); cudaFree(c->dRgba8);
+    c->target[0] = c->target[1] = nullptr; c->dIds = nullptr; c->dRgba8 = nullptr;
+    c->width = c->height = 0;
+    c->accumIndex = 0;
+}
+
+// How many coordinates c in [0, extent) satisfy (c / tileSize) % numTiles == tile.
+int ownedCount(int extent, int tileSize, int numTiles, int tile) {
+    if (tileSize <= 0 || numTiles <= 0 || tile < 0 || tile >= numTiles) return 0;
+    const long long period = (long long)tileSize * numTiles;
+    const long long full = extent / period;
+    long long rest = extent - full * period - (long long)tile * tileSize;
+    rest = std::max(0LL, std::min<long long>(rest, tileSize));
+    return int(full * tileSize + rest);
+}
+
+}  // namespace
+
+extern "C" {
+
+const char* rt_version(void) { return "librt_b200 0.1 (sm_100a)"; }
+
+const char* rt_last_error(rt_ctx* ctx) { return ctx ? ctx->err.c_str() : "null context"; }
+
+int rt_create(rt_ctx** out, int device) {
+    if (!out) return RT_ERR_INVALID;
+    *out = nullptr;
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess || n <= 0) return RT_ERR_CUDA;
+    if (device < 0 || device >= n) return RT_ERR_INVALID;
+    rt_ctx* c = new rt_ctx();
+    c->device = device;
+    Bind bind(c);
+    cudaDeviceProp prop;
+    if (cudaGetDeviceProperties(&prop, device) != cudaSuccess) { delete c; return RT_ERR_CUDA; }
+    c->smCount = prop.multiProcessorCount;
+    if (cudaStreamCreateWithFlags(&c->ownStream, cudaStreamNonBlocking) != cudaSuccess ||
+        cudaEventCreate(&c->ev0) != cudaSuccess || cudaEventCreate(&c->ev1) != cudaSuccess ||
+        cudaMalloc(&c->dCounters, RT_CNT_COUNT * sizeof(unsigned long long)) != cudaSuccess ||
+        cudaMalloc(&c->dWork, sizeof(unsigned int)) != cudaSuccess) {
+        delete c;
+        return RT_ERR_CUDA;
+    }
+    c->stream = c->ownStream;
+    cudaMemset(c->dCounters, 0, RT_CNT_COUNT * sizeof(unsigned long long));
+    *out = c;
+    return RT_OK;
+}
+
+void rt_destroy(rt_ctx* c) {
+    if (!c) return;
+    Bind bind(c);
+    cudaStreamSynchronize(c->stream);
+    freeScene(c);
+    freeTargets(c);
+    cudaFree(c->dCounters); cudaFree(c->dWork);
+    if (c->ev0) cudaEventDestroy(c->ev0);
+    if (c->ev1) cudaEventDestroy(c->ev1);
+    if (c->ownStream) cudaStreamDestroy(c->ownStream);
+    delete c;
+}
+
+int rt_set_stream(rt_ctx* c, void* s) {
+    if (!c) return RT_ERR_INVALID;
+    c->stream = s ? static_cast<cudaStream_t>(s) : c->ownStream;
+    return RT_OK;
+}
+
+int rt_sync(rt_ctx* c) {
+    if (!c) return RT_ERR_INVALID;
+    Bind bind(c);
+    RT_CUDA(c, cudaStreamSynchronize(c->stream));
+    return RT_OK;
+}
+
+int rt_scene_free(rt_ctx* c) {
+    if (!c) return RT_ERR_INVALID;
+    Bind bind(c);
+    cudaStreamSynchronize(c->stream);
+    freeScene(c);
+    return RT_OK;
+}
+
+// scene.py:223-236 — validates the three SSBO payloads, then builds the device layout (rt_types.h):
+// internal nodes in breadth-first order from the root, triangles in leaf order.  Unreachable nodes
+// (the reference's builder leaves dead single-child chains in the array) are dropped.
+int rt_scene_upload(rt_ctx* c, const void* trisV, uint32_t nTris, const void* boxesV, uint32_t nBoxes,
+                    const uint32_t* indices, uint32_t nIndices) {
+    if (!c) return RT_ERR_INVALID;
+    if ((nTris && !trisV) || (nBoxes && !boxesV) || (nIndices && !indices))
+        return fail(c, RT_ERR_INVALID, "rt_scene_upload: null buffer with non-zero count");
+    Bind bind(c);
+    const HostTri* tris = static_cast<const HostTri*>(trisV);
+    const HostBox* boxes = static_cast<const HostBox*>(boxesV);
+
+    std::vector<NodeRec> nodes;
+    std::vector<TriRec> triRecs;
+    std::vector<ShadeRec> shadeRecs;
+    std::vector<uint32_t> triIds;
+    std::vector<uint2> bigLeaves;
+    DeviceScene sc{};
+    sc.rootRef = RT_REF_NONE;
+    sc.stackDepth = 1;
+
+    if (nBoxes > 0) {
+        // 1. reachability, validation, cycle check and height (iterative DFS)
+        std::vector<int8_t> state(nBoxes, 0);          // 0 new, 1 open, 2 done
+        std::vector<int32_t> height(nBoxes, 0);        // internal nodes on the longest path below (incl. self)
+        std::vector<uint32_t> work{0};
+        while (!work.empty()) {
+            const uint32_t i = work.back();
+            const HostBox& b = boxes[i];
+            if (state[i] == 2) { work.pop_back(); continue; }
+            if (b.childA == -1) {                       // leaf to the shader (fragment.glsl:266)
+                if (uint64_t(b.triangleOffset) + b.numTriangles > nIndices)
+                    return fail(c, RT_ERR_INVALID, "box %u: triangle range [%u,+%u) exceeds %u indices", i,
+                                b.triangleOffset, b.numTriangles, nIndices);
+                for (uint32_t k = 0; k < b.numTriangles; k++)
+                    if (indices[b.triangleOffset + k] >= nTris)
+                        return fail(c, RT_ERR_INVALID, "box %u: triangle index %u >= %u", i,
+                                    indices[b.triangleOffset + k], nTris);
+                state[i] = 2; height[i] = 0; work.pop_back();
+                continue;
+            }
+            if (b.childA < 0 || uint32_t(b.childA) >= nBoxes || b.childB < -1 ||
+                (b.childB >= 0 && uint32_t(b.childB) >= nBoxes))
+                return fail(c, RT_ERR_INVALID, "box %u: child index out of range (%d, %d)", i, b.childA, b.childB);
+            const int32_t kids[2] = {b.childA, b.childB};
+            if (state[i] == 0) {
+                state[i] = 1;
+                for (int32_t k : kids) {
+                    if (k < 0) continue;
+                    if (state[k] == 1) return fail(c, RT_ERR_INVALID, "box %u: child %d closes a cycle", i, k);
+                    if (state[k] == 0) work.push_back(uint32_t(k));
+                }
+            } else {
+                int32_t h = 0;
+                for (int32_t k : kids)
+                    if (k >= 0) {
+                        if (state[k] != 2) return fail(c, RT_ERR_INVALID, "box %u: child %d closes a cycle", i, k);
+                        h = std::max(h, height[k]);
+                    }
+                height[i] = h + 1; state[i] = 2; work.pop_back();
+            }
+        }
+        if (height[0] > RT_MAX_STACK)
+            return fail(c, RT_ERR_INVALID, "tree height %d exceeds the traversal stack (%d)", height[0], RT_MAX_STACK);
+        sc.stackDepth = std::max(1, height[0]);
+
+        // 2. numbering: internal nodes breadth-first, leaves in order of first reference
+        std::vector<int32_t> ref(nBoxes, RT_REF_NONE);
+        std::vector<uint32_t> order;
+        auto leafRef = [&](uint32_t i) -> int32_t {
+            const HostBox& b = boxes[i];
+            const uint32_t first = uint32_t(triRecs.size());
+            for (uint32_t k = 0; k < b.numTriangles; k++) {
+                const uint32_t id = indices[b.triangleOffset + k];
+                const HostTri& t = tris[id];
+                // fragment.glsl:112-116, same operation order, no contraction (-ffp-contract=off on the host)
+                volatile float abx = t.v1p[0] - t.v0p[0], aby = t.v1p[1] - t.v0p[1], abz = t.v1p[2] - t.v0p[2];
+                volatile float acx = t.v2p[0] - t.v0p[0], acy = t.v2p[1] - t.v0p[1], acz = t.v2p[2] - t.v0p[2];
+                volatile float m0 = aby * acz, m1 = acy * abz, m2 = abz * acx, m3 = acz * abx, m4 = abx * acy, m5 = acx * aby;
+                TriRec r;
+                r.v0x = t.v0p[0]; r.v0y = t.v0p[1]; r.v0z = t.v0p[2];
+                r.abx = abx; r.aby = aby; r.abz = abz; r.acx = acx; r.acy = acy; r.acz = acz;
+                r.nx = m0 - m1; r.ny = m2 - m3; r.nz = m4 - m5;
+                triRecs.push_back(r);
+                ShadeRec s{};
+                s.n0x = t.v0n[0]; s.n0y = t.v0n[1]; s.n0z = t.v0n[2];
+                s.n1x = t.v1n[0]; s.n1y = t.v1n[1]; s.n1z = t.v1n[2];
+                s.n2x = t.v2n[0]; s.n2y = t.v2n[1]; s.n2z = t.v2n[2];
+                s.colR = t.color[0]; s.colG = t.color[1]; s.colB = t.color[2];
+                s.emcR = t.emc[0]; s.emcG = t.emc[1]; s.emcB = t.emc[2];
+                s.emission = t.surface[0]; s.roughness = t.surface[1];
+                shadeRecs.push_back(s);
+                triIds.push_back(id);
+            }
+            uint32_t code;
+            if (b.numTriangles <= RT_LEAF_MAX) {
+                code = (first << RT_LEAF_BITS) | b.numTriangles;
+            } else {
+                code = (uint32_t(bigLeaves.size()) << RT_LEAF_BITS) | RT_LEAF_BIG;
+                bigLeaves.push_back(make_uint2(first, b.numTriangles));
+            }
+            return int32_t(~code);
+        };
+        auto assign = [&](int32_t child) -> int32_t {
+            if (child < 0) return RT_REF_NONE;
+            if (ref[child] != RT_REF_NONE) return ref[child];
+            if (boxes[child].childA == -1) {
+                ref[child] = leafRef(uint32_t(child));
+            } else {
+                ref[child] = int32_t(order.size());
+                order.push_back(uint32_t(child));
+            }
+            return ref[child];
+        };
+        sc.rootRef = assign(0);
+        for (int k = 0; k < 3; k++) { sc.rootMin[k] = boxes[0].posMin[k]; sc.rootMax[k] = boxes[0].posMax[k]; }
+        nodes.reserve(nBoxes);
+        for (size_t at = 0; at < order.size(); at++) {
+            const HostBox& b = boxes[order[at]];
+            NodeRec n{};
+            n.refA = assign(b.childA);
+            n.refB = assign(b.childB);
+            const HostBox& a = boxes[b.childA];
+            n.aMinX = a.posMin[0]; n.aMinY = a.posMin[1]; n.aMinZ = a.posMin[2];
+            n.aMaxX = a.posMax[0]; n.aMaxY = a.posMax[1]; n.aMaxZ = a.posMax[2];
+            if (b.childB >= 0) {
+                const HostBox& bb = boxes[b.childB];
+                n.bMinX = bb.posMin[0]; n.bMinY = bb.posMin[1]; n.bMinZ = bb.posMin[2];
+                n.bMaxX = bb.posMax[0]; n.bMaxY = bb.posMax[1]; n.bMaxZ = bb.posMax[2];
+            }
+            nodes.push_back(n);
+            if (triRecs.size() >= RT_MAX_SLOTS)
+                return fail(c, RT_ERR_INVALID, "scene needs more than %u triangle slots", RT_MAX_SLOTS);
+        }
+    }
+
+    cudaStreamSynchronize(c->stream);
+    freeScene(c);
+    auto upload = [&](auto** dst, const auto& vec) -> cudaError_t {
+        using T = typename std::remove_reference<decltype(vec)>::type::value_type;
+        const size_t bytes = std::max<size_t>(vec.size(), 1) * sizeof(T);
+        cudaError_t e = cudaMalloc(reinterpret_cast<void**>(dst), bytes);
+        if (e != cudaSuccess) return e;
+        if (!vec.empty()) e = cudaMemcpyAsync(*dst, vec.data(), vec.size() * sizeof(T), cudaMemcpyHostToDevice, c->stream);
+        return e;
+    };
+    RT_CUDA(c, upload(&c->dNodes, nodes));
+    RT_CUDA(c, upload(&c->dTris, triRecs));
+    RT_CUDA(c, upload(&c->dShade, shadeRecs));
+    RT_CUDA(c, upload(&c->dTriId, triIds));
+    RT_CUDA(c, upload(&c->dBig, bigLeaves));
+    RT_CUDA(c, cudaStreamSynchronize(c->stream));   // the host vectors die at return
+    sc.nodes = c->dNodes; sc.tris = c->dTris; sc.shade = c->dShade; sc.triId = c->dTriId; sc.bigLeaves = c->dBig;
+    sc.nNodes = uint32_t(nodes.size());
+    sc.nSlots = uint32_t(triRecs.size());
+    c->scene = sc;
+    c->haveScene = true;
+    return RT_OK;
+}
+
+int rt_set_params(rt_ctx* c, const rt_params* p) {
+    if (!c || !p) return RT_ERR_INVALID;
+    if (p->tileSizeX <= 0 || p->tileSizeY <= 0 || p->numTilesX <= 0 || p->numTilesY <= 0)
+        return fail(c, RT_ERR_INVALID, "tile sizes and counts must be positive (the shader divides by them)");
+    if (p->nBounces < 0 || p->rays_per_pixel < 0) return fail(c, RT_ERR_INVALID, "negative nBounces / rays_per_pixel");
+    c->params = *p;
+    c->haveParams = true;
+    return RT_OK;
+}
+
+int rt_set_variant(rt_ctx* c, int variant) {
+    if (!c) return RT_ERR_INVALID;
+    if (variant < RT_VARIANT_AUTO || variant > RT_VARIANT_WAVEFRONT) return fail(c, RT_ERR_INVALID, "unknown variant %d", variant);
+    c->variant = variant;
+    return RT_OK;
+}
+
+int rt_target_free(rt_ctx* c) {
+    if (!c) return RT_ERR_INVALID;
+    Bind bind(c);
+    cudaStreamSynchronize(c->stream);
+    freeTargets(c);
+    return RT_OK;
+}
+
+int rt_target_clear(rt_ctx* c) {
+    if (!c) return RT_ERR_INVALID;
+    if (!c->target[0]) return fail(c, RT_ERR_STATE, "no target");
+    Bind bind(c);
+    const size_t n = size_t(c->width) * c->height;
+    RT_CUDA(c, cudaMemsetAsync(c->target[0], 0, n * sizeof(float4), c->stream));
+    RT_CUDA(c, cudaMemsetAsync(c->target[1], 0, n * sizeof(float4), c->stream));
+    RT_CUDA(c, cudaMemsetAsync(c->dIds, 0xff, n * sizeof(int32_t), c->stream));
+    c->accumIndex = 0;   // main.py:262
+    return RT_OK;
+}
+
+int rt_target_create(rt_ctx* c, int width, int height) {
+    if (!c) return RT_ERR_INVALID;
+    if (width <= 0 || height <= 0) return fail(c, RT_ERR_INVALID, "target size %d x %d", width, height);
+    Bind bind(c);
+    cudaStreamSynchronize(c->stream);
+    freeTargets(c);
+    const size_t n = size_t(width) * height;
+    if (cudaMalloc(&c->target[0], n * sizeof(float4)) != cudaSuccess || cudaMalloc(&c->target[1], n * sizeof(float4)) != cudaSuccess ||
+        cudaMalloc(&c->dIds, n * sizeof(int32_t)) != cudaSuccess || cudaMalloc(&c->dRgba8, n * sizeof(uchar4)) != cudaSuccess) {
+        freeTargets(c);
+        cudaGetLastError();
+        return fail(c, RT_ERR_NOMEM, "cannot allocate %d x %d targets", width, height);
+    }
+    c->width = width; c->height = height;
+    return rt_target_clear(c);
+}
+
+}  // extern "C"
+
+namespace {
+
+// One draw (main.py:376-394, 401): read target[accumIndex], write the other, flip.
+// sumMode: 0 = the shader's running mean; 1 = next = curr; 2 = next = prev + curr.
+int renderPass(rt_ctx* c, int frameNumber, int tileX, int tileY, int flags, int sumMode) {
+    if (!c->haveScene) return fail(c, RT_ERR_STATE, "rt_render_pass before rt_scene_upload");
+    if (!c->haveParams) return fail(c, RT_ERR_STATE, "rt_render_pass before rt_set_params");
+    if (!c->target[0]) return fail(c, RT_ERR_STATE, "rt_render_pass before rt_target_create");
+    const rt_params& u = c->params;
+    PassParams P{};
+    P.scene = c->scene;
+    P.tileX = tileX; P.tileY = tileY; P.tileSizeX = u.tileSizeX; P.tileSizeY = u.tileSizeY;
+    P.numTilesX = u.numTilesX; P.numTilesY = u.numTilesY;
+    P.lambertian = u.lambertian; P.nBounces = u.nBounces; P.raysPerPixel = u.rays_per_pixel; P.frameNumber = frameNumber;
+    P.skyBrightness = u.skyBrightness; P.xStep = u.xStep; P.yStep = u.yStep; P.dirStartX = u.dirStartX;
+    P.dirStartY = u.dirStartY; P.jitterAmount = u.jitterAmount;
+    for (int k = 0; k < 3; k++) {
+        P.camPos[k] = u.camPos[k]; P.camRight[k] = u.camRight[k]; P.camUp[k] = u.camUp[k]; P.camForward[k] = u.camForward[k];
+    }
+    P.width = c->width; P.height = c->height;
+    const int prev = c->accumIndex, next = 1 - prev;
+    P.prev = c->target[prev]; P.next = c->target[next];
+    P.primaryIds = (flags & RT_PASS_PRIMARY_IDS) ? c->dIds : nullptr;
+    P.counters = (flags & RT_PASS_COUNTERS) ? c->dCounters : nullptr;
+    P.ownedW = ownedCount(c->width, u.tileSizeX, u.numTilesX, tileX);
+    P.ownedH = ownedCount(c->height, u.tileSizeY, u.numTilesY, tileY);
+    P.sumMode = sumMode;
+    P.workCounter = c->dWork;
+    const bool covers = P.ownedW == c->width && P.ownedH == c->height;
+    if (!covers && !(flags & RT_PASS_SKIP_MASKED)) {
+        // pixels outside the tile keep the previous target's texel, all four channels (fragment.glsl:382-386)
+        RT_CUDA(c, cudaMemcpyAsync(c->target[next], c->target[prev], size_t(c->width) * c->height * sizeof(float4),
+                                   cudaMemcpyDeviceToDevice, c->stream));
+    }
+    cudaError_t e;
+    if (c->variant == RT_VARIANT_PERSISTENT)
+        e = rtLaunchPersistent(P, P.counters != nullptr, P.primaryIds != nullptr, c->smCount, c->stream);
+    else
+        e = rtLaunchPixel(P, P.counters != nullptr, P.primaryIds != nullptr, c->stream);
+    if (e != cudaSuccess) return fail(c, RT_ERR_CUDA, "kernel launch: %s", cudaGetErrorString(e));
+    c->accumIndex = next;
+    return RT_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int rt_render_pass_ex(rt_ctx* c, int frameNumber, int tileX, int tileY, int flags) {
+    if (!c) return RT_ERR_INVALID;
+    Bind bind(c);
+    return renderPass(c, frameNumber, tileX, tileY, flags, 0);
+}
+
+int rt_render_pass(rt_ctx* c, int frameNumber, int tileX, int tileY) {
+    return rt_render_pass_ex(c, frameNumber, tileX, tileY, RT_PASS_DEFAULT);
+}
+
+// main.py:409-430: tileX fastest, then tileY, then the frame counter.
+int rt_render_frames(rt_ctx* c, int firstFrame, int nFrames) {
+    if (!c) return RT_ERR_INVALID;
+    if (!c->haveParams) return fail(c, RT_ERR_STATE, "rt_render_frames before rt_set_params");
+    Bind bind(c);
+    for (int f = firstFrame; f < firstFrame + nFrames; f++)
+        for (int ty = 0; ty < c->params.numTilesY; ty++)
+            for (int tx = 0; tx < c->params.numTilesX; tx++) {
+                const int rc = renderPass(c, f, tx, ty, RT_PASS_DEFAULT, 0);
+                if (rc != RT_OK) return rc;
+            }
+    return RT_OK;
+}
+
+// Frame-sharded progressive mode: this context renders frames firstFrame,
+// firstFrame + stride, ... of tile (params.tileX, params.tileY) and keeps their SUM; the owner of the
+// image adds the shares (NCCL reduce) and calls rt_finish_sum.  Masked pixels are left untouched.
+int rt_render_frames_sum(rt_ctx* c, int firstFrame, int nFrames, int stride) {
+    if (!c) return RT_ERR_INVALID;
+    if (!c->haveParams) return fail(c, RT_ERR_STATE, "rt_render_frames_sum before rt_set_params");
+    if (stride <= 0) return fail(c, RT_ERR_INVALID, "frame stride must be positive");
+    Bind bind(c);
+    for (int k = 0; k < nFrames; k++) {
+        const int rc = renderPass(c, firstFrame + k * stride, c->params.tileX, c->params.tileY, RT_PASS_SKIP_MASKED, k == 0 ? 1 : 2);
+        if (rc != RT_OK) return rc;
+    }
+    return RT_OK;
+}
+
+int rt_finish_sum(rt_ctx* c, int totalFrames) {
+    if (!c) return RT_ERR_INVALID;
+    if (!c->target[0]) return fail(c, RT_ERR_STATE, "no target");
+    if (totalFrames <= 0) return fail(c, RT_ERR_INVALID, "total_frames must be positive");
+    Bind bind(c);
+    RT_CUDA(c, rtLaunchFinishSum(c->target[c->accumIndex], size_t(c->width) * c->height, float(totalFrames), c->stream));
+    return RT_OK;
+}
+
+int rt_read_accum_f32(rt_ctx* c, float* dst) {
+    if (!c || !dst) return RT_ERR_INVALID;
+    if (!c->target[0]) return fail(c, RT_ERR_STATE, "no target");
+    Bind bind(c);
+    RT_CUDA(c, cudaMemcpyAsync(dst, c->target[c->accumIndex], size_t(c->width) * c->height * sizeof(float4),
+                               cudaMemcpyDeviceToHost, c->stream));
+    RT_CUDA(c, cudaStreamSynchronize(c->stream));
+    return RT_OK;
+}
+
+int rt_read_rgba8(rt_ctx* c, uint8_t* dst) {
+    if (!c || !dst) return RT_ERR_INVALID;
+    if (!c->target[0]) return fail(c, RT_ERR_STATE, "no target");
+    Bind bind(c);
+    const size_t n = size_t(c->width) * c->height;
+    RT_CUDA(c, rtLaunchToRgba8(c->target[c->accumIndex], c->dRgba8, n, c->stream));
+    RT_CUDA(c, cudaMemcpyAsync(dst, c->dRgba8, n * sizeof(uchar4), cudaMemcpyDeviceToHost, c->stream));
+    RT_CUDA(c, cudaStreamSynchronize(c->stream));
+    return RT_OK;
+}
+
+int rt_read_primary_ids(rt_ctx* c, int32_t* dst) {
+    if (!c || !dst) return RT_ERR_INVALID;
+    if (!c->dIds) return fail(c, RT_ERR_STATE, "no target");
+    Bind bind(c);
+    RT_CUDA(c, cudaMemcpyAsync(dst, c->dIds, size_t(c->width) * c->height * sizeof(int32_t), cudaMemcpyDeviceToHost, c->stream));
+    RT_CUDA(c, cudaStreamSynchronize(c->stream));
+    return RT_OK;
+}
+
+int rt_read_counters(rt_ctx* c, uint64_t* dst, int n) {
+    if (!c || !dst || n < 0) return RT_ERR_INVALID;
+    Bind bind(c);
+    unsigned long long host[RT_CNT_COUNT];
+    RT_CUDA(c, cudaMemcpyAsync(host, c->dCounters, sizeof host, cudaMemcpyDeviceToHost, c->stream));
+    RT_CUDA(c, cudaStreamSynchronize(c->stream));
+    for (int k = 0; k < n; k++) dst[k] = k < RT_CNT_COUNT ? host[k] : 0;
+    return RT_OK;
+}
+
+int rt_reset_counters(rt_ctx* c) {
+    if (!c) return RT_ERR_INVALID;
+    Bind bind(c);
+    RT_CUDA(c, cudaMemsetAsync(c->dCounters, 0, RT_CNT_COUNT * sizeof(unsigned long long), c->stream));
+    return RT_OK;
+}
+
+void* rt_accum_device_ptr(rt_ctx* c, int which) {
+    if (!c || !c->target[0]) return nullptr;
+    if (which < 0) which = c->accumIndex;
+    return which <= 1 ? c->target[which] : nullptr;
+}
+
+int rt_accum_index(rt_ctx* c) { return c ? c->accumIndex : RT_ERR_INVALID; }
+
+int rt_set_accum_index(rt_ctx* c, int index) {
+    if (!c || (index != 0 && index != 1)) return RT_ERR_INVALID;
+    c->accumIndex = index;
+    return RT_OK;
+}
+
+int rt_band_rows(rt_ctx* c, int tileY) {
+    if (!c) return RT_ERR_INVALID;
+    if (!c->haveParams || !c->target[0]) return fail(c, RT_ERR_STATE, "rt_band_rows needs params and a target");
+    return ownedCount(c->height, c->params.tileSizeY, c->params.numTilesY, tileY);
+}
+
+static int bandCopy(rt_ctx* c, int tileY, void* dense, int toDense) {
+    if (!c || !dense) return RT_ERR_INVALID;
+    if (!c->haveParams || !c->target[0]) return fail(c, RT_ERR_STATE, "band copy needs params and a target");
+    Bind bind(c);
+    const int rows = ownedCount(c->height, c->params.tileSizeY, c->params.numTilesY, tileY);
+    RT_CUDA(c, rtLaunchBandCopy(c->target[c->accumIndex], static_cast<float4*>(dense), c->width, rows, c->params.tileSizeY,
+                                c->params.numTilesY, tileY, toDense, c->stream));
+    return RT_OK;
+}
+
+int rt_band_gather(rt_ctx* c, int tileY, void* dense) { return bandCopy(c, tileY, dense, 1); }
+int rt_band_scatter(rt_ctx* c, int tileY, const void* dense) { return bandCopy(c, tileY, const_cast<void*>(dense), 0); }
+
+int rt_timer_start(rt_ctx* c) {
+    if (!c) return RT_ERR_INVALID;
+    Bind bind(c);
+    RT_CUDA(c, cudaEventRecord(c->ev0, c->stream));
+    return RT_OK;
+}
+
+int rt_timer_stop(rt_ctx* c, float* ms) {
+    if (!c || !ms) return RT_ERR_INVALID;
+    Bind bind(c);
+    RT_CUDA(c, cudaEventRecord(c->ev1, c->stream));
+    RT_CUDA(c, cudaEventSynchronize(c->ev1));
+    RT_CUDA(c, cudaEventElapsedTime(ms, c->ev0, c->ev1));
+    return RT_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,185 @@
+// rt_device.cuh — device-side arithmetic of the reference's shaders/fragment.glsl, restated for sm_100a.
+//
+// Numeric contract (identical to oracle/rt_oracle.cpp, which the parity tests
+// compare against bit for bit): IEEE binary32, round-to-nearest-even, NO contraction — every product
+// and sum below is an explicit __fmul_rn / __fadd_rn so the result does not depend on -fmad; division
+// and square root are the correctly rounded __fdiv_rn / __frcp_rn / __fsqrt_rn (1/x correctly rounded is
+// unique, so __frcp_rn(x) == 1.0f / x); min/max are fminf/fmaxf (FMNMX: a NaN operand is ignored).
+// dot = (x*x' + y*y') + z*z'; cross(a,b) = (a.y*b.z - b.y*a.z, a.z*b.x - b.z*a.x, a.x*b.y - b.x*a.y).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "rt_types.h"
+
+#define RT_DEV __device__ __forceinline__
+
+struct f3 {
+    float x, y, z;
+};
+
+RT_DEV f3 mk3(float x, float y, float z) { f3 r; r.x = x; r.y = y; r.z = z; return r; }
+RT_DEV float mul(float a, float b) { return __fmul_rn(a, b); }
+RT_DEV float add(float a, float b) { return __fadd_rn(a, b); }
+RT_DEV float sub(float a, float b) { return __fsub_rn(a, b); }
+RT_DEV f3 add3(f3 a, f3 b) { return mk3(add(a.x, b.x), add(a.y, b.y), add(a.z, b.z)); }
+RT_DEV f3 sub3(f3 a, f3 b) { return mk3(sub(a.x, b.x), sub(a.y, b.y), sub(a.z, b.z)); }
+RT_DEV f3 mul3(f3 a, f3 b) { return mk3(mul(a.x, b.x), mul(a.y, b.y), mul(a.z, b.z)); }
+RT_DEV f3 scale3(f3 a, float s) { return mk3(mul(a.x, s), mul(a.y, s), mul(a.z, s)); }
+RT_DEV f3 neg3(f3 a) { return mk3(-a.x, -a.y, -a.z); }
+RT_DEV float dot3(f3 a, f3 b) { return add(add(mul(a.x, b.x), mul(a.y, b.y)), mul(a.z, b.z)); }
+RT_DEV f3 cross3(f3 a, f3 b) {
+    return mk3(sub(mul(a.y, b.z), mul(b.y, a.z)), sub(mul(a.z, b.x), mul(b.z, a.x)),
+               sub(mul(a.x, b.y), mul(b.x, a.y)));
+}
+RT_DEV float length3(f3 v) { return __fsqrt_rn(dot3(v, v)); }
+RT_DEV f3 div3(f3 a, float s) { return mk3(__fdiv_rn(a.x, s), __fdiv_rn(a.y, s), __fdiv_rn(a.z, s)); }
+RT_DEV f3 normalize3(f3 v) { return div3(v, length3(v)); }
+RT_DEV f3 ld3(const float* p) { return mk3(p[0], p[1], p[2]); }
+
+// fragment.glsl:206-218.  float(result)/2^32*2-1: the scalings are exact, so one rounding at the -1.
+RT_DEV float randomValue(uint32_t& state) {
+    state = state * 747796405u + 2891336453u;
+    uint32_t t = state >> ((state >> 28u) + 4u);
+    uint32_t result = (t ^ state) * 277803737u;
+    result = (result >> 22u) ^ result;
+    float f = __uint2float_rn(result);
+    return sub(mul(mul(f, 2.3283064365386963e-10f), 2.0f), 1.0f);
+}
+
+// fragment.glsl:181-204 with invDir hoisted per ray (bit-identical: same operands, same operations).
+RT_DEV float slabTest(f3 o, f3 inv, float minX, float minY, float minZ, float maxX, float maxY, float maxZ) {
+    float tx0 = mul(sub(minX, o.x), inv.x), tx1 = mul(sub(maxX, o.x), inv.x);
+    float ty0 = mul(sub(minY, o.y), inv.y), ty1 = mul(sub(maxY, o.y), inv.y);
+    float tz0 = mul(sub(minZ, o.z), inv.z), tz1 = mul(sub(maxZ, o.z), inv.z);
+    float dstNear = fmaxf(fmaxf(fminf(tx0, tx1), fminf(ty0, ty1)), fminf(tz0, tz1));
+    float dstFar = fminf(fminf(fmaxf(tx0, tx1), fmaxf(ty0, ty1)), fmaxf(tz0, tz1));
+    float r = -1.0f;
+    if (dstFar >= dstNear) {
+        if (!(dstFar < 0.0f)) r = (dstNear < 0.0f) ? 0.0f : dstNear;
+    }
+    return r;
+}
+
+struct RayHit {
+    float t, u, v;
+    int32_t slot;     // triangle slot of the closest hit, -1 = miss
+};
+
+struct WorkCount {
+    uint32_t internal, leaves, tris, pops;
+};
+
+// Shared-memory traversal stack: entry e of thread t lives at stackBase[e * blockDim.x + t], an 8-byte
+// (ref, tNear) pair — lanes touch consecutive 8-byte words, so a push/pop is conflict-free.
+struct StackRef {
+    uint2* base;
+    uint32_t stride;
+};
+
+// fragment.glsl:106-147 up to the acceptance test, on a precomputed TriRec.  Returns true when the
+// shader would have taken this candidate (h.didHit && h.t < closestT && h.t > 1e-6).
+RT_DEV bool triangleTest(const TriRec* __restrict__ rec, f3 o, f3 d, float closestT, float& tOut, float& uOut,
+                         float& vOut) {
+    const float4 q0 = __ldg(reinterpret_cast<const float4*>(rec));
+    const float4 q1 = __ldg(reinterpret_cast<const float4*>(rec) + 1);
+    const float4 q2 = __ldg(reinterpret_cast<const float4*>(rec) + 2);
+    const float EPS = 1e-6f;
+    f3 v0 = mk3(q0.x, q0.y, q0.z), eAB = mk3(q0.w, q1.x, q1.y), eAC = mk3(q1.z, q1.w, q2.x);
+    f3 N = mk3(q2.y, q2.z, q2.w);
+    float det = dot3(d, N);
+    if (fabsf(det) < EPS) return false;
+    float invDet = __frcp_rn(det);
+    f3 ao = sub3(o, v0);
+    float t = mul(-dot3(ao, N), invDet);
+    if (t <= EPS) return false;
+    f3 dao = cross3(ao, d);
+    float u = mul(-dot3(eAC, dao), invDet);
+    float v = mul(dot3(eAB, dao), invDet);
+    if (u < 0.0f || v < 0.0f || add(u, v) > 1.0f) return false;
+    if (!(t < closestT && t > 1e-6f)) return false;
+    tOut = t; uOut = u; vOut = v;
+    return true;
+}
+
+// fragment.glsl:246-307.  Same visiting order and the same accept/cull comparisons as the shader:
+//  * a node's tNear is computed once (when its parent is expanded) and carried on the stack; the pop-time
+//    cull `tNear > closestT` uses the closestT current at the pop, as in the shader (:261-262);
+//  * the nearer child (tA < tB strictly; on a tie B first, :292-297) is visited next without a round trip
+//    through the stack — it would have been popped immediately;
+//  * an entry already farther than closestT when pushed can never survive its pop (closestT only
+//    shrinks), so it is not pushed; the POPS counter still counts it.
+template <bool COUNT>
+RT_DEV RayHit traverse(const DeviceScene& sc, f3 o, f3 d, StackRef st, WorkCount& wc) {
+    RayHit best;
+    best.t = 1e30f; best.u = 0.f; best.v = 0.f; best.slot = -1;
+    f3 inv = mk3(__frcp_rn(d.x), __frcp_rn(d.y), __frcp_rn(d.z));
+    uint32_t sp = 0;
+    int32_t cur = sc.rootRef;
+    {
+        float tRoot = slabTest(o, inv, sc.rootMin[0], sc.rootMin[1], sc.rootMin[2], sc.rootMax[0], sc.rootMax[1],
+                               sc.rootMax[2]);
+        if (COUNT) wc.pops++;
+        if (tRoot < 0.0f || tRoot > best.t) return best;
+    }
+    const uint32_t tid = threadIdx.x;
+    for (;;) {
+        if (cur >= 0) {
+            // internal node: slab-test both children (:281-287)
+            const float4* np = reinterpret_cast<const float4*>(sc.nodes + cur);
+            const float4 q0 = __ldg(np), q1 = __ldg(np + 1), q2 = __ldg(np + 2);
+            const int4 q3 = __ldg(reinterpret_cast<const int4*>(np + 3));
+            if (COUNT) wc.internal++;
+            float tA = -1.0f, tB = -1.0f;
+            if (q3.x != RT_REF_NONE) tA = slabTest(o, inv, q0.x, q0.y, q0.z, q0.w, q1.x, q1.y);
+            if (q3.y != RT_REF_NONE) tB = slabTest(o, inv, q1.z, q1.w, q2.x, q2.y, q2.z, q2.w);
+            const bool hitA = tA >= 0.0f, hitB = tB >= 0.0f;
+            int32_t nearRef, farRef; float nearT, farT; bool haveFar = false, haveNear = true;
+            if (hitA && hitB) {
+                const bool aFirst = tA < tB;
+                nearRef = aFirst ? q3.x : q3.y; nearT = aFirst ? tA : tB;
+                farRef = aFirst ? q3.y : q3.x;  farT = aFirst ? tB : tA;
+                haveFar = true;
+                if (COUNT) wc.pops += 2;
+            } else if (hitA) {
+                nearRef = q3.x; nearT = tA; farRef = 0; farT = 0.f;
+                if (COUNT) wc.pops++;
+            } else if (hitB) {
+                nearRef = q3.y; nearT = tB; farRef = 0; farT = 0.f;
+                if (COUNT) wc.pops++;
+            } else {
+                haveNear = false; nearRef = 0; nearT = 0.f; farRef = 0; farT = 0.f;
+            }
+            if (haveFar && !(farT > best.t)) {
+                st.base[sp * st.stride + tid] = make_uint2(uint32_t(farRef), __float_as_uint(farT));
+                sp++;
+            }
+            if (haveNear && !(nearT > best.t)) { cur = nearRef; continue; }
+        } else {
+            // leaf: every triangle in slot order, first found wins ties (:266-279)
+            uint32_t code = uint32_t(~cur);
+            uint32_t count = code & ((1u << RT_LEAF_BITS) - 1u);
+            uint32_t first = code >> RT_LEAF_BITS;
+            if (count == RT_LEAF_BIG) {
+                const uint2 big = __ldg(sc.bigLeaves + first);
+                first = big.x; count = big.y;
+            }
+            if (COUNT) { wc.leaves++; wc.tris += count; }
+            for (uint32_t k = 0; k < count; k++) {
+                float t, u, v;
+                if (triangleTest(sc.tris + first + k, o, d, best.t, t, u, v)) {
+                    best.t = t; best.u = u; best.v = v; best.slot = int32_t(first + k);
+                }
+            }
+        }
+        // pop (:256-262)
+        for (;;) {
+            if (sp == 0) return best;
+            sp--;
+            const uint2 e = st.base[sp * st.stride + tid];
+            if (__uint_as_float(e.y) > best.t) continue;
+            cur = int32_t(e.x);
+            break;
+        }
+    }
+}

@@ -1,0 +1,263 @@
+// rt_kernels.cu — sm_100a kernels of librt_b200: the per-pixel loop of the reference's fragment.glsl.
+//
+// Variant PIXEL: one thread per owned pixel, the whole pixel-frame (rays_per_pixel paths of up to
+// nBounces rays, RNG state carried across the samples — fragment.glsl:352-366 makes them sequentially
+// dependent) in one kernel.  A warp covers an 8x4 pixel tile so primary rays are coherent.  Traversal
+// stacks live in shared memory ((ref, tNear) pairs, entry-major so lanes are conflict-free); scene
+// records come through the read-only path as 16-byte loads; the scene (<= 8 MB) is L2-resident.
+#include <cuda_runtime.h>
+
+#include "../../include/rt_b200.h"
+#include "rt_shade.cuh"
+
+namespace {
+
+constexpr int kBlockThreads = 128;   // 4 warps: 16 x 8 pixel block, each warp an 8 x 4 tile
+
+struct PathCounters {
+    uint32_t v[RT_CNT_COUNT];
+};
+
+// One pixel-frame: fragment.glsl main() from :388 on.  Returns the pixel's colour for this frame.
+template <bool COUNT, bool IDS>
+RT_DEV f3 pixelFrame(const PassParams& P, int px, int py, StackRef st, PathCounters& pc, int32_t& primaryId) {
+    const DeviceScene& sc = P.scene;
+    uint32_t seed;
+    const f3 camPos = ld3(P.camPos);
+    const f3 primaryDir = primaryDirection(P, px, py, seed);
+    const f3 sky = scale3(mk3(0.1f, 0.6f, 0.92f), P.skyBrightness);   // :242-244, :388
+    const bool lambertian = P.lambertian != 0;
+
+    // The primary ray is the same for every sample of the pixel-frame (:361-362): trace it once.
+    WorkCount primaryWork = {0, 0, 0, 0};
+    RayHit primaryHit;
+    primaryHit.slot = -1; primaryHit.t = 0.f; primaryHit.u = 0.f; primaryHit.v = 0.f;
+    if (P.nBounces > 0 && P.raysPerPixel > 0) {
+        primaryHit = traverse<COUNT>(sc, camPos, primaryDir, st, primaryWork);
+        if (COUNT) pc.v[RT_CNT_RAYS_TRACED]++;
+    }
+    if (IDS) primaryId = primaryHit.slot >= 0 ? int32_t(__ldg(sc.triId + primaryHit.slot)) : -1;
+
+    f3 color = mk3(0.f, 0.f, 0.f);
+    for (int s = 0; s < P.raysPerPixel; s++) {
+        // raytrace(), fragment.glsl:309-350
+        f3 incoming = mk3(0.f, 0.f, 0.f), rayColor = mk3(1.f, 1.f, 1.f);
+        f3 o = camPos, d = primaryDir;
+        if (COUNT) pc.v[RT_CNT_PATHS]++;
+        for (int i = 0; i < P.nBounces; i++) {
+            RayHit h;
+            if (i == 0) {
+                h = primaryHit;
+                if (COUNT) {
+                    pc.v[RT_CNT_INTERNAL] += primaryWork.internal; pc.v[RT_CNT_LEAVES] += primaryWork.leaves;
+                    pc.v[RT_CNT_TRI_TESTS] += primaryWork.tris;    pc.v[RT_CNT_POPS] += primaryWork.pops;
+                }
+            } else {
+                WorkCount wc = {0, 0, 0, 0};
+                h = traverse<COUNT>(sc, o, d, st, wc);
+                if (COUNT) {
+                    pc.v[RT_CNT_RAYS_TRACED]++;
+                    pc.v[RT_CNT_INTERNAL] += wc.internal; pc.v[RT_CNT_LEAVES] += wc.leaves;
+                    pc.v[RT_CNT_TRI_TESTS] += wc.tris;    pc.v[RT_CNT_POPS] += wc.pops;
+                }
+            }
+            if (COUNT) pc.v[RT_CNT_RAYS]++;
+            if (h.slot >= 0) {
+                if (COUNT) pc.v[RT_CNT_HITS]++;
+                const SurfaceHit hit = resolveHit(sc, h, o, d);
+                const f3 dDiff = diffuseDir(hit.normal, seed, lambertian);
+                const f3 dSpec = reflect3(d, hit.normal);
+                d = lerpDir(dDiff, dSpec, hit.roughness);
+                o = add3(hit.point, scale3(hit.normal, 1e-4f));
+                f3 emitted = scale3(hit.emissionColor, hit.emission);
+                if (lambertian) emitted = scale3(emitted, 2.0f);
+                incoming = add3(incoming, mul3(emitted, rayColor));
+                rayColor = mul3(rayColor, hit.color);
+                if (hit.emission > 0.0f) break;
+            } else {
+                incoming = add3(incoming, sky);   // un-attenuated, as the shader does (:343)
+                break;
+            }
+        }
+        color = add3(color, incoming);
+    }
+    return div3(color, float(P.raysPerPixel));   // :365
+}
+
+template <bool COUNT>
+RT_DEV void flushCounters(const PassParams& P, PathCounters& pc) {
+    if constexpr (COUNT) {
+#pragma unroll
+        for (int k = 0; k < RT_CNT_COUNT; k++) {
+            unsigned long long v = pc.v[k];
+#pragma unroll
+            for (int off = 16; off > 0; off >>= 1) v += __shfl_xor_sync(0xffffffffu, v, off);
+            if ((threadIdx.x & 31) == 0 && v) atomicAdd(P.counters + k, v);
+        }
+    }
+}
+
+template <bool COUNT, bool IDS>
+__global__ void __launch_bounds__(kBlockThreads) rtPixelKernel(const __grid_constant__ PassParams P) {
+    extern __shared__ uint2 stackMem[];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int ox = blockIdx.x * 16 + (warp & 1) * 8 + (lane & 7);
+    const int oy = blockIdx.y * 8 + (warp >> 1) * 4 + (lane >> 3);
+    const bool valid = ox < P.ownedW && oy < P.ownedH;
+    PathCounters pc;
+#pragma unroll
+    for (int k = 0; k < RT_CNT_COUNT; k++) pc.v[k] = 0;
+    if (valid) {
+        const int px = ownedToPixel(ox, P.tileSizeX, P.numTilesX, P.tileX);
+        const int py = ownedToPixel(oy, P.tileSizeY, P.numTilesY, P.tileY);
+        StackRef st;
+        st.base = stackMem; st.stride = kBlockThreads;
+        int32_t primaryId = -1;
+        const f3 curr = pixelFrame<COUNT, IDS>(P, px, py, st, pc, primaryId);
+        const size_t at = size_t(py) * size_t(P.width) + size_t(px);
+        P.next[at] = accumulate(P, curr, at);
+        if (IDS) P.primaryIds[at] = primaryId;
+    }
+    flushCounters<COUNT>(P, pc);
+}
+
+// Variant PERSISTENT: as many CTAs as fit the machine; each warp claims 8x4 pixel tiles from a global
+// counter (one atomic per warp, broadcast by shuffle) until the frame is exhausted.  Removes the tail
+// effect of a fixed pixel->CTA mapping when per-pixel cost varies by orders of magnitude (sky vs mesh).
+template <bool COUNT, bool IDS>
+__global__ void __launch_bounds__(kBlockThreads) rtPersistentKernel(const __grid_constant__ PassParams P) {
+    extern __shared__ uint2 stackMem[];
+    const int lane = threadIdx.x & 31;
+    const int tilesX = (P.ownedW + 7) >> 3, tilesY = (P.ownedH + 3) >> 2;
+    const unsigned int nTiles = (unsigned int)tilesX * (unsigned int)tilesY;
+    PathCounters pc;
+#pragma unroll
+    for (int k = 0; k < RT_CNT_COUNT; k++) pc.v[k] = 0;
+    StackRef st;
+    st.base = stackMem; st.stride = kBlockThreads;
+    for (;;) {
+        unsigned int tile = 0;
+        if (lane == 0) tile = atomicAdd(P.workCounter, 1u);
+        tile = __shfl_sync(0xffffffffu, tile, 0);
+        if (tile >= nTiles) break;
+        const int ox = int(tile % (unsigned int)tilesX) * 8 + (lane & 7);
+        const int oy = int(tile / (unsigned int)tilesX) * 4 + (lane >> 3);
+        if (ox < P.ownedW && oy < P.ownedH) {
+            const int px = ownedToPixel(ox, P.tileSizeX, P.numTilesX, P.tileX);
+            const int py = ownedToPixel(oy, P.tileSizeY, P.numTilesY, P.tileY);
+            int32_t primaryId = -1;
+            const f3 curr = pixelFrame<COUNT, IDS>(P, px, py, st, pc, primaryId);
+            const size_t at = size_t(py) * size_t(P.width) + size_t(px);
+            P.next[at] = accumulate(P, curr, at);
+            if (IDS) P.primaryIds[at] = primaryId;
+        }
+        __syncwarp();
+    }
+    flushCounters<COUNT>(P, pc);
+}
+
+// ---------------------------------------------------------------------------------- utility kernels
+// glReadPixels(GL_RGBA, GL_UNSIGNED_BYTE) of an RGBA32F target (main.py:434): clamp to [0,1], scale by
+// 255, round to nearest.  NaN clamps to 0.
+__global__ void rtToRgba8Kernel(const float4* __restrict__ src, uchar4* __restrict__ dst, size_t n) {
+    size_t i = size_t(blockIdx.x) * blockDim.x + threadIdx.x;
+    const size_t step = size_t(gridDim.x) * blockDim.x;
+    for (; i < n; i += step) {
+        const float4 p = src[i];
+        auto conv = [](float x) -> unsigned char {
+            x = (x != x) ? 0.0f : fminf(fmaxf(x, 0.0f), 1.0f);
+            return (unsigned char)floorf(__fadd_rn(__fmul_rn(x, 255.0f), 0.5f));
+        };
+        dst[i] = make_uchar4(conv(p.x), conv(p.y), conv(p.z), conv(p.w));
+    }
+}
+
+// Rows owned by tile row `tile` <-> dense buffer (multi-GPU band sharding).
+__global__ void rtBandCopyKernel(float4* __restrict__ target, float4* __restrict__ dense, int width, int rows,
+                                 int tileSizeY, int numTilesY, int tile, int toDense) {
+    const size_t n = size_t(rows) * size_t(width);
+    size_t i = size_t(blockIdx.x) * blockDim.x + threadIdx.x;
+    const size_t step = size_t(gridDim.x) * blockDim.x;
+    for (; i < n; i += step) {
+        const int k = int(i / size_t(width)), x = int(i % size_t(width));
+        const int y = (numTilesY == 1) ? k : (k / tileSizeY) * (numTilesY * tileSizeY) + tile * tileSizeY + (k % tileSizeY);
+        const size_t at = size_t(y) * size_t(width) + size_t(x);
+        if (toDense) dense[i] = target[at];
+        else target[at] = dense[i];
+    }
+}
+
+// After the frame-sharded reduce: the target holds the SUM of total frames -> mean (IEEE division, alpha 1).
+__global__ void rtFinishSumKernel(float4* __restrict__ target, size_t n, float frames) {
+    size_t i = size_t(blockIdx.x) * blockDim.x + threadIdx.x;
+    const size_t step = size_t(gridDim.x) * blockDim.x;
+    for (; i < n; i += step) {
+        float4 p = target[i];
+        p.x = __fdiv_rn(p.x, frames); p.y = __fdiv_rn(p.y, frames); p.z = __fdiv_rn(p.z, frames); p.w = 1.0f;
+        target[i] = p;
+    }
+}
+
+}  // namespace
+
+// ------------------------------------------------------------------------------------- launchers
+// (C++ linkage, called from rt_api.cu)
+size_t rtPixelKernelSmem(int stackDepth) { return size_t(stackDepth) * kBlockThreads * sizeof(uint2); }
+
+cudaError_t rtLaunchPixel(const PassParams& P, bool count, bool ids, cudaStream_t stream) {
+    dim3 grid((P.ownedW + 15) / 16, (P.ownedH + 7) / 8);
+    if (grid.x == 0 || grid.y == 0) return cudaSuccess;
+    const size_t smem = rtPixelKernelSmem(P.scene.stackDepth);
+#define RT_LAUNCH(C, I)                                                                                   \
+    do {                                                                                                  \
+        if (smem > 48 * 1024)                                                                             \
+            cudaFuncSetAttribute(rtPixelKernel<C, I>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)); \
+        rtPixelKernel<C, I><<<grid, kBlockThreads, smem, stream>>>(P);                                   \
+    } while (0)
+    if (count && ids) RT_LAUNCH(true, true);
+    else if (count) RT_LAUNCH(true, false);
+    else if (ids) RT_LAUNCH(false, true);
+    else RT_LAUNCH(false, false);
+#undef RT_LAUNCH
+    return cudaGetLastError();
+}
+
+cudaError_t rtLaunchPersistent(const PassParams& P, bool count, bool ids, int sms, cudaStream_t stream) {
+    if (P.ownedW <= 0 || P.ownedH <= 0) return cudaSuccess;
+    const size_t smem = rtPixelKernelSmem(P.scene.stackDepth);
+    cudaError_t e = cudaMemsetAsync(P.workCounter, 0, sizeof(unsigned int), stream);
+    if (e != cudaSuccess) return e;
+#define RT_LAUNCH(C, I)                                                                                        \
+    do {                                                                                                       \
+        if (smem > 48 * 1024)                                                                                  \
+            cudaFuncSetAttribute(rtPersistentKernel<C, I>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)); \
+        int perSm = 0;                                                                                         \
+        e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSm, rtPersistentKernel<C, I>, kBlockThreads, smem); \
+        if (e != cudaSuccess) return e;                                                                        \
+        if (perSm < 1) perSm = 1;                                                                              \
+        rtPersistentKernel<C, I><<<sms * perSm, kBlockThreads, smem, stream>>>(P);                            \
+    } while (0)
+    if (count && ids) RT_LAUNCH(true, true);
+    else if (count) RT_LAUNCH(true, false);
+    else if (ids) RT_LAUNCH(false, true);
+    else RT_LAUNCH(false, false);
+#undef RT_LAUNCH
+    return cudaGetLastError();
+}
+
+cudaError_t rtLaunchToRgba8(const float4* src, uchar4* dst, size_t n, cudaStream_t stream) {
+    rtToRgba8Kernel<<<148 * 8, 256, 0, stream>>>(src, dst, n);
+    return cudaGetLastError();
+}
+
+cudaError_t rtLaunchBandCopy(float4* target, float4* dense, int width, int rows, int tileSizeY, int numTilesY,
+                             int tile, int toDense, cudaStream_t stream) {
+    if (rows <= 0) return cudaSuccess;
+    rtBandCopyKernel<<<148 * 8, 256, 0, stream>>>(target, dense, width, rows, tileSizeY, numTilesY, tile, toDense);
+    return cudaGetLastError();
+}
+
+cudaError_t rtLaunchFinishSum(float4* target, size_t n, float frames, cudaStream_t stream) {
+    rtFinishSumKernel<<<148 * 8, 256, 0, stream>>>(target, n, frames);
+    return cudaGetLastError();
+}

@@ -1,0 +1,83 @@
+// rt_types.h — device-side data layout of librt_b200 (private to the library).
+//
+// The reference uploads three SSBOs (fragment.glsl:94-104): tris[] 144 B, boundingBoxes[] 48 B,
+// triangleIndices[] u32.  rt_scene_upload re-lays them out, bit-preservingly, so the
+// traversal touches only what it needs, with 16-byte vector loads through the read-only path:
+//
+//   NodeRec  64 B  one per REACHABLE internal node: the bounds of BOTH children (the shader slab-tests
+//                  both children when it expands a node, fragment.glsl:285-287) + two child references.
+//                  A popped node's own bounds are never re-fetched: its tNear travels with the stack
+//                  entry (the re-test at fragment.glsl:261 recomputes the same value from the same inputs).
+//   TriRec   48 B  one per triangle slot, in leaf order (removes the triangleIndices indirection):
+//                  v0, eAB = v1-v0, eAC = v2-v0, N = cross(eAB,eAC), all computed on the host with the
+//                  shader's operation order and no contraction (fragment.glsl:112-116).
+//   ShadeRec 80 B  one per triangle slot: the three vertex normals + material, fetched once per ray for
+//                  the winning triangle only (the shader copies them for every candidate, :151-173).
+//   triId    4 B   per slot: the original triangle index (primary-id image only).
+//
+// Child reference (int32): >= 0 : index of an internal NodeRec
+//                          <  0 : leaf, ~ref = (first_slot << RT_LEAF_BITS) | count,  count in [1, RT_LEAF_MAX]
+//                                 count == RT_LEAF_BIG means: first_slot indexes bigLeaves[] = {first, count}
+//                          RT_REF_NONE : absent child (never hit)
+#pragma once
+#include <stdint.h>
+
+#define RT_LEAF_BITS 6
+#define RT_LEAF_BIG 63
+#define RT_LEAF_MAX 62
+#define RT_REF_NONE 0x7fffffff
+#define RT_MAX_SLOTS (1u << (31 - RT_LEAF_BITS))
+#define RT_MAX_STACK 64
+
+struct alignas(16) NodeRec {
+    float aMinX, aMinY, aMinZ, aMaxX;
+    float aMaxY, aMaxZ, bMinX, bMinY;
+    float bMinZ, bMaxX, bMaxY, bMaxZ;
+    int32_t refA, refB, pad0, pad1;
+};
+
+struct alignas(16) TriRec {
+    float v0x, v0y, v0z, abx;
+    float aby, abz, acx, acy;
+    float acz, nx, ny, nz;
+};
+
+struct alignas(16) ShadeRec {
+    float n0x, n0y, n0z, n1x;
+    float n1y, n1z, n2x, n2y;
+    float n2z, colR, colG, colB;
+    float emcR, emcG, emcB, emission;
+    float roughness, pad0, pad1, pad2;
+};
+
+struct DeviceScene {
+    const NodeRec* nodes;
+    const TriRec* tris;
+    const ShadeRec* shade;
+    const uint32_t* triId;
+    const uint2* bigLeaves;
+    float rootMin[3], rootMax[3];   // the root's own bounds (slab-tested once per ray, fragment.glsl:253-262)
+    int32_t rootRef;
+    int32_t stackDepth;             // entries a traversal can need (tree depth + 1)
+    uint32_t nNodes, nSlots;
+};
+
+// Everything a pass needs, passed by value as a __grid_constant__ kernel parameter.
+struct PassParams {
+    DeviceScene scene;
+    // uniform block (fragment.glsl:7-38)
+    int32_t tileX, tileY, tileSizeX, tileSizeY, numTilesX, numTilesY;
+    int32_t lambertian, nBounces, raysPerPixel, frameNumber;
+    float skyBrightness, xStep, yStep, dirStartX, dirStartY, jitterAmount;
+    float camPos[3], camRight[3], camUp[3], camForward[3];
+    // targets
+    int32_t width, height;
+    const float4* prev;
+    float4* next;
+    int32_t* primaryIds;            // nullable
+    unsigned long long* counters;   // nullable (RT_CNT_COUNT entries)
+    // compact launch domain: the pixels of this tile only
+    int32_t ownedW, ownedH;
+    int32_t sumMode;                // 1: next = prev + curr (frame-sharded progressive mode), 0: running mean
+    unsigned int* workCounter;      // persistent variant
+};
