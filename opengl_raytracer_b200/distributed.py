@@ -1,0 +1,89 @@
+"""Multi-GPU host logic: one process per GPU, torch.distributed for the plumbing.
+
+The path shards two ways, both taken from the reference's own mechanisms:
+
+* **tile mode** (one frame, many GPUs) — the shader's tile mask (fragment.glsl:382) with ``numTilesX = 1``,
+  ``numTilesY = world`` and ``tileSizeY = band_rows`` makes rank g own the interleaved row bands
+  ``(y // band_rows) % world == g``: load-balanced, and each pixel is computed exactly as on one GPU, so the
+  assembled frame is bit-identical.  Exchange step: rank 0 gathers every rank's dense band buffer
+  (``rt_band_gather`` -> NCCL gather -> ``rt_band_scatter``).
+* **frame mode** (progressive accumulation) — frames are independent (the seed depends on px, py and
+  frameNumber only, fragment.glsl:390): rank g renders frames g, g+world, ... as a running SUM
+  (``rt_render_frames_sum``), the sums are added with an NCCL reduce and rank 0 divides by the frame count
+  (``rt_finish_sum``).  Differs from the sequential running mean only by float re-association.
+
+Samples inside one pixel-frame are never split: the RNG state is carried across them (fragment.glsl:358-363).
+The functions take the renderer as an object with the rtlib.Context methods they call, so the CPU tests can
+drive the same logic with gloo and a stand-in renderer.
+"""
+from __future__ import annotations
+
+import numpy as np
+
+
+def band_params(params, rank: int, world: int, band_rows: int = 8):
+    """Uniform block for rank ``rank`` of ``world`` in tile mode."""
+    return params.replace(tileSizeX=params.width, numTilesX=1, tileX=0,
+                          tileSizeY=band_rows, numTilesY=world, tileY=rank)
+
+
+def band_row_indices(height: int, band_rows: int, world: int, rank: int) -> np.ndarray:
+    """Rows y of the frame owned by ``rank``: (y // band_rows) % world == rank, ascending."""
+    y = np.arange(height)
+    return y[(y // band_rows) % world == rank]
+
+
+def max_band_rows(height: int, band_rows: int, world: int) -> int:
+    return max(len(band_row_indices(height, band_rows, world, r)) for r in range(world))
+
+
+def frame_share(first_frame: int, n_frames: int, rank: int, world: int):
+    """(first, count, stride) of the frames rank renders in frame mode."""
+    count = (n_frames - rank + world - 1) // world if n_frames > rank else 0
+    return first_frame + rank, count, world
+
+
+def gather_bands(dist, local_dense, rank: int, world: int, dst: int = 0):
+    """Gather equally sized (padded) dense band buffers to ``dst``; returns the list on dst, else None."""
+    import torch
+    if world == 1:
+        return [local_dense]
+    bufs = [torch.empty_like(local_dense) for _ in range(world)] if rank == dst else None
+    dist.gather(local_dense, gather_list=bufs, dst=dst)
+    return bufs
+
+
+def render_tile_mode(ctx, dist, params, rank: int, world: int, frame: int = 0, band_rows: int = 8, dense=None):
+    """One frame in tile mode.  ``ctx`` already holds the scene and a width x height target.  Returns the
+    dense buffer used (reusable); on rank 0 the current target then holds the whole frame."""
+    import torch
+    p = band_params(params, rank, world, band_rows)
+    ctx.set_params(p)
+    ctx.render_pass(frame, 0, rank, flags=4)                    # RT_PASS_SKIP_MASKED
+    if world == 1:
+        return dense
+    rows = max_band_rows(params.height, band_rows, world)
+    if dense is None:
+        dense = torch.empty((rows, params.width, 4), dtype=torch.float32, device="cuda")
+    ctx.band_gather(rank, dense.data_ptr())
+    bufs = gather_bands(dist, dense, rank, world)
+    if rank == 0:
+        for g in range(1, world):
+            ctx.band_scatter(g, bufs[g].data_ptr())
+    return dense
+
+
+def render_frame_mode(ctx, dist, params, rank: int, world: int, first_frame: int, n_frames: int, accum_tensor):
+    """Progressive accumulation sharded by frames.  ``accum_tensor(ctx)`` returns a torch view of the current
+    target; after the reduce rank 0's target holds the mean of all frames."""
+    first, count, stride = frame_share(first_frame, n_frames, rank, world)
+    ctx.set_params(params)
+    if count:
+        ctx.render_frames_sum(first, count, stride)
+    view = accum_tensor(ctx)
+    if count == 0:
+        view.zero_()
+    if world > 1:
+        dist.reduce(view, dst=0)
+    if rank == 0:
+        ctx.finish_sum(n_frames)

@@ -279,3 +279,22 @@ class Context:
         ms = ctypes.c_float()
         self._check(self.lib.rt_timer_stop(self.handle, ctypes.byref(ms)))
         return ms.value
+
+    def use_torch_stream(self):
+        """Run on torch's current CUDA stream so torch events and NCCL collectives order with the kernels."""
+        import torch
+        self.set_stream(torch.cuda.current_stream().cuda_stream)
+
+    def accum_tensor(self, which: int = -1):
+        """Zero-copy torch view (H, W, 4) float32 of an accumulation target (optional tensor hand-off)."""
+        import torch
+
+        class _Dev:
+            pass
+
+        holder = _Dev()
+        holder.__cuda_array_interface__ = {
+            "shape": (self.height, self.width, 4), "typestr": "<f4", "version": 3,
+            "data": (self.accum_device_ptr(which), False), "strides": None,
+        }
+        return torch.as_tensor(holder, device=f"cuda:{self.device}")
