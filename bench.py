@@ -1,0 +1,377 @@
+#!/usr/bin/env python
+"""bench.py — BASELINE.json's metric (Mrays/s and ms/frame, dragon 3840x2160, 64 spp, 4 bounces) on N B200s.
+
+    python bench.py --gpus 1 --steps K --warmup W             # one process per GPU (torchrun for N > 1)
+    python bench.py --impl reference ...                      # the reference's shader math on the host cores
+
+A *step* is one whole frame of the workload: 3840 x 2160 pixels x 64 samples per pixel x up to 5 rays per
+path (bounces = 4 -> nBounces = 5), scene models/dragon under open sky as BASELINE.json names it.  A *ray*
+is one raycast() (fragment.glsl:246) actually traversed; the primary ray of a pixel-frame is traversed once
+and reused by its 64 samples (they share it, fragment.glsl:361-362), so traced rays < reference-equivalent
+rays — both are reported, the headline uses traced rays.
+
+N > 1: tile mode — rank g owns the interleaved 8-row bands (y // 8) % N == g of the SAME frame (strong
+scaling), the bands are gathered to rank 0 over NCCL inside the timed region.
+
+JSON keys beyond the contract: "roofline" (dominant kernel, algorithmic scene bytes per ray from SURVEY §8d
+against the measured HBM peak — the scene is L2-resident by design, so this is an L2/issue-bound path and the
+fraction can exceed 1; "issue" carries the warp-instruction roofline), "cpu_baseline", "box_variant" (same
+frame size with the dragon inside the reference's closed room: the realistic-throughput figure).
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+import numpy as np  # noqa: E402
+
+from opengl_raytracer_b200 import configs  # noqa: E402
+from opengl_raytracer_b200.scene import Scene  # noqa: E402
+
+WORKLOAD = "cfg4_open"
+BOX_WORKLOAD = "cfg4_box"
+METRIC = "Mrays/s"
+BAND_ROWS = 8
+
+
+def load_peaks():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.isfile(path):
+        with open(path) as f:
+            d = json.load(f)
+        return float(d["hbm_gbs"]), "measured (MEASURED_PEAKS.json)", float(d.get("sm_max_mhz", 1965.0))
+    return 6650.0, "fallback (B200_PROFILING.md)", 1965.0
+
+
+def algorithmic_bytes(cnt, traced_fraction=1.0):
+    """64 B per expanded internal node + 16 B per leaf entered + 40 B per triangle test + 68 B per
+    hit + 24 B (root bounds) per ray.  ``cnt`` are reference-equivalent counters; scaled to traced rays."""
+    b = 64 * cnt["internal"] + 16 * cnt["leaves"] + 40 * cnt["tri_tests"] + 68 * cnt["hits"] + 24 * cnt["rays"]
+    return b * traced_fraction
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled during the timed region."""
+    FIELDS = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+              "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+              "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index, self.rows, self.proc = index, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.FIELDS}",
+                                          "--format=csv,noheader,nounits", "-lms", "200"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            threading.Thread(target=self._pump, daemon=True).start()
+        except OSError:
+            self.proc = None
+
+    def _pump(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def stop(self):
+        if self.proc:
+            self.proc.terminate()
+        sm, mx, reasons = [], [], set()
+        names = ("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap")
+        for r in self.rows:
+            try:
+                sm.append(float(r[0])); mx.append(float(r[1]))
+            except (ValueError, IndexError):
+                continue
+            for name, v in zip(names, r[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def build_scene(name):
+    cfg = configs.scene_configs()[name]
+    tris, boxes, indices = Scene(configs.build_objects(cfg.objects)).pack()
+    return cfg, tris, boxes, indices
+
+
+# ------------------------------------------------------------------------------------ reference arm
+def run_reference(args):
+    """The reference's own shader math on the host cores: oracle/_ref (fragment.glsl compiled as C++) when it
+    was built, else the hand-written port.  A step is a bounded sample of the workload: one sample per pixel
+    of the same 4K frame on every `stride`-th 8-row band (frameNumber = step), all host threads."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    import oracle
+    kind = "reference" if oracle.have_ref() else "port"
+    impl = "ref" if kind == "reference" else "port"
+    if not os.path.isfile(oracle.PORT_LIB):
+        oracle.build_port()
+    cfg, tris, boxes, indices = build_scene(WORKLOAD)
+    params = cfg.params(rays_per_pixel=1)
+    stride = args.cpu_band_stride
+    sample = params.replace(tileSizeX=cfg.width, numTilesX=1, tileSizeY=BAND_ROWS, numTilesY=stride, tileY=0)
+    rays, secs = [], []
+    for step in range(args.warmup + args.steps):
+        p = sample.replace(frameNumber=step)
+        t0 = time.perf_counter()
+        oracle.render_pass(tris, boxes, indices, p, impl=impl)
+        dt = time.perf_counter() - t0
+        if step >= args.warmup:
+            _, _, cnt = oracle.render_pass(tris, boxes, indices, p, impl="port", want_counters=True)   # untimed count
+            rays.append(cnt["rays"]); secs.append(dt)
+    value = sum(rays) / sum(secs) / 1e6
+    cores = oracle.num_threads(impl)
+    desc = (f"{WORKLOAD}: 1 sample/pixel on every {stride}th {BAND_ROWS}-row band of the 3840x2160 frame "
+            f"({sum(rays) // len(rays)} rays/step), frameNumber = step")
+    line = {"impl": "reference", "metric": METRIC, "value": value, "unit": "Mrays/s", "n_gpus": args.gpus,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * sum(secs) / len(secs),
+            "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": f"{WORKLOAD}: models/dragon, 3840x2160, 64 spp, 4 bounces (bounded sample, see cpu_baseline.sample)"},
+            "cpu_baseline": {"value": value, "unit": "Mrays/s", "cores": cores, "kind": kind, "sample": desc},
+            "e2e": {"value": value, "unit": "Mrays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}
+    print(json.dumps(line), flush=True)
+
+
+# ------------------------------------------------------------------------------------------ GPU arm
+def run_gpu(args):
+    import torch
+    import torch.distributed as dist
+
+    from opengl_raytracer_b200 import distributed, rtlib
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if world != args.gpus and world > 1:
+        raise SystemExit(f"--gpus {args.gpus} but WORLD_SIZE={world}")
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    dev = torch.device("cuda", local)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def max_over_ranks(x):
+        t = torch.tensor([x], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    def sum_over_ranks(vec):
+        t = torch.tensor(vec, dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.SUM)
+        return [float(x) for x in t.tolist()]
+
+    ctx = rtlib.Context(local)
+    ctx.use_torch_stream()
+    ctx.set_variant(args.variant)
+    flush_buf = torch.empty(256 << 20, dtype=torch.uint8, device=dev)     # > 126 MB L2
+    peak_gbs, peak_src, sm_max = load_peaks()
+
+    def measure(name, steps, warmup, with_e2e):
+        cfg, tris, boxes, indices = build_scene(name)
+        if args.spp:
+            cfg = cfg.scaled(cfg.width, cfg.height, args.spp)
+        params = cfg.params()
+        # pinned host staging for the end-to-end leg
+        host = {}
+        for key, arr in (("tris", tris), ("boxes", boxes), ("indices", indices)):
+            t = torch.empty(arr.nbytes, dtype=torch.uint8).pin_memory()
+            t.numpy()[:] = arr.view(np.uint8).reshape(-1)
+            host[key] = t
+        out_host = torch.empty((cfg.height, cfg.width, 4), dtype=torch.float32).pin_memory()
+        n_tris, n_boxes = len(tris), len(boxes)
+
+        def upload():
+            ctx._check(ctx.lib.rt_scene_upload(ctx.handle, host["tris"].data_ptr(), n_tris, host["boxes"].data_ptr(),
+                                               n_boxes, host["indices"].data_ptr(), indices.size))
+
+        upload()
+        ctx.set_params(params)
+        ctx.target_create(cfg.width, cfg.height)
+        dense = None
+
+        def step(frame=0):
+            nonlocal dense
+            ctx.target_clear()
+            dense = distributed.render_tile_mode(ctx, dist, params, rank, world, frame, BAND_ROWS, dense)
+
+        # work counters of one step (untimed; reference-equivalent counts, rays_traced = actual traversals)
+        ctx.reset_counters()
+        ctx.set_params(distributed.band_params(params, rank, world, BAND_ROWS))
+        ctx.target_clear()
+        ctx.render_pass(0, 0, rank, flags=rtlib.PASS_COUNTERS | rtlib.PASS_SKIP_MASKED)
+        mine = ctx.read_counters()
+        total = dict(zip(rtlib.COUNTER_NAMES, sum_over_ranks([mine[k] for k in rtlib.COUNTER_NAMES])))
+        local_alg_bytes = algorithmic_bytes(mine, mine["rays_traced"] / max(mine["rays"], 1))
+
+        for _ in range(warmup):
+            step()
+        sampler = ClockSampler(local)
+        if rank == 0:
+            sampler.start()
+        kernel_events = []
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(steps):
+            flush_buf.zero_()                                   # L2 flush between steps (inside the timed region)
+            ctx.target_clear()
+            ctx.set_params(distributed.band_params(params, rank, world, BAND_ROWS))
+            k0, k1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            k0.record()
+            ctx.render_pass(0, 0, rank, flags=rtlib.PASS_SKIP_MASKED)
+            k1.record()
+            kernel_events.append((k0, k1))
+            if world > 1:
+                rows = distributed.max_band_rows(cfg.height, BAND_ROWS, world)
+                if dense is None:
+                    dense = torch.empty((rows, cfg.width, 4), dtype=torch.float32, device=dev)
+                ctx.band_gather(rank, dense.data_ptr())
+                bufs = distributed.gather_bands(dist, dense, rank, world)
+                if rank == 0:
+                    for g in range(1, world):
+                        ctx.band_scatter(g, bufs[g].data_ptr())
+        e1.record()
+        barrier()
+        clocks = sampler.stop() if rank == 0 else None
+        ms_total = max_over_ranks(e0.elapsed_time(e1))
+        kernel_ms = float(np.mean([a.elapsed_time(b) for a, b in kernel_events]))
+        ms_step = ms_total / steps
+        res = {"cfg": cfg, "counters": total, "ms_per_step": ms_step, "kernel_ms": kernel_ms,
+               "mrays_s": total["rays_traced"] / (ms_step * 1e-3) / 1e6,
+               "ref_equiv_mrays_s": total["rays"] / (ms_step * 1e-3) / 1e6, "clocks": clocks,
+               "local_alg_bytes": local_alg_bytes, "launches": steps}
+        if with_e2e:
+            # end to end through the C ABI with HOST buffers: scene upload (H2D), uniforms, draw, gather, and the
+            # RGBA32F read-back (D2H) on rank 0, every step
+            def e2e_step():
+                upload()
+                step()
+                if rank == 0:
+                    ctx._check(ctx.lib.rt_read_accum_f32(ctx.handle, out_host.data_ptr()))
+            for _ in range(max(1, warmup // 2)):
+                e2e_step()
+            barrier()
+            t0 = time.perf_counter()
+            for _ in range(steps):
+                e2e_step()
+            barrier()
+            e2e_ms = max_over_ranks((time.perf_counter() - t0) * 1e3) / steps
+            res["e2e"] = {"value": total["rays_traced"] / (e2e_ms * 1e-3) / 1e6, "unit": "Mrays/s",
+                          "ms_per_step": e2e_ms,
+                          "h2d_bytes_per_step": int(tris.nbytes + boxes.nbytes + indices.nbytes),
+                          "d2h_bytes_per_step": int(out_host.numel() * 4)}
+            res["e2e_launches"] = steps
+        res["scene"] = (tris, boxes, indices)
+        return res
+
+    main = measure(WORKLOAD, args.steps, args.warmup, True)
+    cfg = main["cfg"]
+    cnt = main["counters"]
+    achieved = main["local_alg_bytes"] / (main["kernel_ms"] * 1e-3) / 1e9
+    traffic = None
+    tpath = os.path.join(ROOT, "profiles", "traffic.json")
+    if os.path.isfile(tpath):
+        with open(tpath) as f:
+            traffic = json.load(f).get(WORKLOAD, {}).get("dram_bytes_per_launch")
+    roofline = {"bound": "hbm", "achieved": achieved, "peak": peak_gbs, "unit": "GB/s", "frac": achieved / peak_gbs,
+                "traffic": traffic, "peak_source": peak_src, "kernel": "rtPersistentKernel" if args.variant == "persistent" else "rtPixelKernel",
+                "kernel_ms": main["kernel_ms"],
+                "note": "algorithmic scene bytes (SURVEY §8d: 64 B/internal node, 16 B/leaf, 40 B/triangle test, 68 B/hit, "
+                        "24 B/ray) consumed per second by this rank's launch; the scene (8 MB) is L2/L1-resident so DRAM "
+                        "traffic is the framebuffer only and the binding limits are L1/L2 latency and warp issue"}
+    line = {"metric": METRIC, "value": main["mrays_s"], "unit": "Mrays/s", "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": main["ms_per_step"], "higher_is_better": True, "scaling": "strong",
+            "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": f"{WORKLOAD}: models/dragon (37,986 triangles) under open sky, {cfg.width}x{cfg.height}, "
+                                   f"{cfg.rays_per_pixel} spp, {cfg.bounces} bounces, 1 frame",
+                       "parallelism": f"tile mode: {world} x interleaved {BAND_ROWS}-row bands, NCCL gather to rank 0",
+                       "l2": "256 MiB memset between steps, inside the timed region", "variant": args.variant},
+            "ms_per_frame": main["ms_per_step"], "rays_per_step": cnt["rays_traced"],
+            "reference_equivalent": {"rays_per_step": cnt["rays"], "mrays_s": main["ref_equiv_mrays_s"]},
+            "e2e": main["e2e"], "gpu_launches": main["launches"], "roofline": roofline, "clocks": main["clocks"]}
+
+    if world == 1 and not args.no_cpu:
+        line["cpu_baseline"] = cpu_baseline(ctx, rtlib, main, args)
+    if not args.no_box:
+        box = measure(BOX_WORKLOAD, max(1, args.steps // 2), 1, False)
+        bc = box["counters"]
+        line["box_variant"] = {"workload": f"{BOX_WORKLOAD}: dragon inside the main.py room, same size/spp/bounces",
+                               "value": box["mrays_s"], "unit": "Mrays/s", "ms_per_frame": box["ms_per_step"],
+                               "rays_per_step": bc["rays_traced"], "kernel_ms": box["kernel_ms"],
+                               "roofline_achieved_gbs": box["local_alg_bytes"] / (box["kernel_ms"] * 1e-3) / 1e9,
+                               "per_ray": {"internal": bc["internal"] / bc["rays"], "tri_tests": bc["tri_tests"] / bc["rays"]}}
+    if rank == 0:
+        print(json.dumps(line), flush=True)
+    ctx.close()
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def cpu_baseline(ctx, rtlib, main, args):
+    """The reference shader (oracle/_ref, else the port) on the host cores: whole 4K frames of the workload at
+    one sample per pixel (frameNumber 0, 1, ...) until about `cpu_seconds` of CPU work; rays counted by a GPU
+    counting pass of the same frames (same rays: the parity tests pin the counters to the oracle's)."""
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    import oracle
+    kind = "reference" if oracle.have_ref() else "port"
+    impl = "ref" if kind == "reference" else "port"
+    if not os.path.isfile(oracle.PORT_LIB):
+        oracle.build_port()
+    cfg = main["cfg"]
+    tris, boxes, indices = main["scene"]
+    params = cfg.params(rays_per_pixel=1)
+    ctx.set_params(params)
+    secs, rays, frames = 0.0, 0, 0
+    while secs < args.cpu_seconds and frames < 64:
+        p = params.replace(frameNumber=frames)
+        t0 = time.perf_counter()
+        oracle.render_pass(tris, boxes, indices, p, impl=impl)
+        secs += time.perf_counter() - t0
+        ctx.reset_counters(); ctx.target_clear()
+        ctx.render_pass(frames, 0, 0, flags=rtlib.PASS_COUNTERS)
+        rays += ctx.read_counters()["rays"]
+        frames += 1
+    return {"value": rays / secs / 1e6, "unit": "Mrays/s", "cores": oracle.num_threads(impl), "kind": kind,
+            "sample": f"{frames} full {cfg.width}x{cfg.height} frame(s) of {WORKLOAD} at 1 sample/pixel "
+                      f"({rays} rays, {secs:.1f} s)"}
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--variant", default="auto", choices=["auto", "pixel", "persistent", "wavefront"])
+    ap.add_argument("--spp", type=int, default=0, help="override samples per pixel (not a valid bench number)")
+    ap.add_argument("--no-box", action="store_true")
+    ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--cpu-seconds", type=float, default=12.0)
+    ap.add_argument("--cpu-band-stride", type=int, default=1)
+    args = ap.parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_gpu(args)
+
+
+if __name__ == "__main__":
+    main()

@@ -116,6 +116,10 @@ RT_DEV RayHit traverse(const DeviceScene& sc, f3 o, f3 d, StackRef st, WorkCount
     f3 inv = mk3(__frcp_rn(d.x), __frcp_rn(d.y), __frcp_rn(d.z));
     uint32_t sp = 0;
     int32_t cur = sc.rootRef;
+    if (cur == RT_REF_NONE) {          // empty scene: the shader's root index fails its bounds check (:259)
+        if (COUNT) wc.pops++;
+        return best;
+    }
     {
         float tRoot = slabTest(o, inv, sc.rootMin[0], sc.rootMin[1], sc.rootMin[2], sc.rootMax[0], sc.rootMax[1],
                                sc.rootMax[2]);

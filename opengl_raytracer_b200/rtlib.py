@@ -283,7 +283,10 @@ class Context:
     def use_torch_stream(self):
         """Run on torch's current CUDA stream so torch events and NCCL collectives order with the kernels."""
         import torch
-        self.set_stream(torch.cuda.current_stream().cuda_stream)
+        handle = torch.cuda.current_stream().cuda_stream
+        # torch reports the legacy default stream as 0, which rt_set_stream reads as "back to the context's own
+        # stream"; cudaStreamLegacy (0x1) is the explicit handle of that stream
+        self.set_stream(handle if handle else 1)
 
     def accum_tensor(self, which: int = -1):
         """Zero-copy torch view (H, W, 4) float32 of an accumulation target (optional tensor hand-off)."""
