@@ -9,6 +9,7 @@
 #include <cstdarg>
 #include <cstdio>
 #include <cstring>
+#include <limits>
 #include <string>
 #include <vector>
 
@@ -314,6 +315,10 @@ int rt_scene_upload(rt_ctx* c, const void* trisV, uint32_t nTris, const void* bo
                 const HostBox& bb = boxes[b.childB];
                 n.bMinX = bb.posMin[0]; n.bMinY = bb.posMin[1]; n.bMinZ = bb.posMin[2];
                 n.bMaxX = bb.posMax[0]; n.bMaxY = bb.posMax[1]; n.bMaxZ = bb.posMax[2];
+            } else {
+                // absent child (fragment.glsl:287 leaves tB = -1): NaN bounds can never pass the slab test
+                const float nan = std::numeric_limits<float>::quiet_NaN();
+                n.bMinX = n.bMinY = n.bMinZ = n.bMaxX = n.bMaxY = n.bMaxZ = nan;
             }
             nodes.push_back(n);
             if (triRecs.size() >= RT_MAX_SLOTS)

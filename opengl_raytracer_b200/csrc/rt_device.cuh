@@ -48,17 +48,19 @@ RT_DEV float randomValue(uint32_t& state) {
 }
 
 // fragment.glsl:181-204 with invDir hoisted per ray (bit-identical: same operands, same operations).
-RT_DEV float slabTest(f3 o, f3 inv, float minX, float minY, float minZ, float maxX, float maxY, float maxZ) {
-    float tx0 = mul(sub(minX, o.x), inv.x), tx1 = mul(sub(maxX, o.x), inv.x);
-    float ty0 = mul(sub(minY, o.y), inv.y), ty1 = mul(sub(maxY, o.y), inv.y);
-    float tz0 = mul(sub(minZ, o.z), inv.z), tz1 = mul(sub(maxZ, o.z), inv.z);
-    float dstNear = fmaxf(fmaxf(fminf(tx0, tx1), fminf(ty0, ty1)), fminf(tz0, tz1));
-    float dstFar = fminf(fminf(fmaxf(tx0, tx1), fmaxf(ty0, ty1)), fmaxf(tz0, tz1));
-    float r = -1.0f;
-    if (dstFar >= dstNear) {
-        if (!(dstFar < 0.0f)) r = (dstNear < 0.0f) ? 0.0f : dstNear;
-    }
-    return r;
+// Returns the entry distance max(dstNear, 0) and sets `hit` to (dstFar >= dstNear && !(dstFar < 0)), which
+// equals dstFar >= max(dstNear, 0): dstNear can only be NaN when every slab value is NaN, and then dstFar
+// is NaN too and the comparison is false, as in the shader.  (The sign of a zero distance is not observable:
+// the value is only compared.)
+RT_DEV float slabTest(f3 o, f3 inv, float minX, float minY, float minZ, float maxX, float maxY, float maxZ, bool& hit) {
+    const float tx0 = mul(sub(minX, o.x), inv.x), tx1 = mul(sub(maxX, o.x), inv.x);
+    const float ty0 = mul(sub(minY, o.y), inv.y), ty1 = mul(sub(maxY, o.y), inv.y);
+    const float tz0 = mul(sub(minZ, o.z), inv.z), tz1 = mul(sub(maxZ, o.z), inv.z);
+    const float dstNear = fmaxf(fmaxf(fminf(tx0, tx1), fminf(ty0, ty1)), fminf(tz0, tz1));
+    const float dstFar = fminf(fminf(fmaxf(tx0, tx1), fmaxf(ty0, ty1)), fmaxf(tz0, tz1));
+    const float entry = fmaxf(dstNear, 0.0f);
+    hit = dstFar >= entry;
+    return entry;
 }
 
 struct RayHit {
@@ -78,28 +80,32 @@ struct StackRef {
 };
 
 // fragment.glsl:106-147 up to the acceptance test, on a precomputed TriRec.  Returns true when the
-// shader would have taken this candidate (h.didHit && h.t < closestT && h.t > 1e-6).
+// shader would have taken this candidate (h.didHit && h.t < closestT && h.t > 1e-6).  The shader's early
+// returns are folded into one predicate; each comparison is the shader's own (NaN-faithful): reject when
+// abs(det) < EPS, t <= EPS, u < 0, v < 0 or u + v > 1.  Values computed past a rejected test are unused
+// (1/det of a tiny det may be inf/NaN — harmless, the predicate is already false).
 RT_DEV bool triangleTest(const TriRec* __restrict__ rec, f3 o, f3 d, float closestT, float& tOut, float& uOut,
                          float& vOut) {
     const float4 q0 = __ldg(reinterpret_cast<const float4*>(rec));
     const float4 q1 = __ldg(reinterpret_cast<const float4*>(rec) + 1);
     const float4 q2 = __ldg(reinterpret_cast<const float4*>(rec) + 2);
     const float EPS = 1e-6f;
-    f3 v0 = mk3(q0.x, q0.y, q0.z), eAB = mk3(q0.w, q1.x, q1.y), eAC = mk3(q1.z, q1.w, q2.x);
-    f3 N = mk3(q2.y, q2.z, q2.w);
-    float det = dot3(d, N);
-    if (fabsf(det) < EPS) return false;
-    float invDet = __frcp_rn(det);
-    f3 ao = sub3(o, v0);
-    float t = mul(-dot3(ao, N), invDet);
-    if (t <= EPS) return false;
-    f3 dao = cross3(ao, d);
-    float u = mul(-dot3(eAC, dao), invDet);
-    float v = mul(dot3(eAB, dao), invDet);
-    if (u < 0.0f || v < 0.0f || add(u, v) > 1.0f) return false;
-    if (!(t < closestT && t > 1e-6f)) return false;
-    tOut = t; uOut = u; vOut = v;
-    return true;
+    const f3 v0 = mk3(q0.x, q0.y, q0.z), eAB = mk3(q0.w, q1.x, q1.y), eAC = mk3(q1.z, q1.w, q2.x);
+    const f3 N = mk3(q2.y, q2.z, q2.w);
+    const float det = dot3(d, N);
+    bool ok = !(fabsf(det) < EPS);
+    const float invDet = __frcp_rn(det);
+    const f3 ao = sub3(o, v0);
+    const float t = mul(-dot3(ao, N), invDet);
+    ok = ok && !(t <= EPS) && (t < closestT && t > 1e-6f);
+    if (ok) {
+        const f3 dao = cross3(ao, d);
+        const float u = mul(-dot3(eAC, dao), invDet);
+        const float v = mul(dot3(eAB, dao), invDet);
+        ok = !(u < 0.0f || v < 0.0f || add(u, v) > 1.0f);
+        tOut = t; uOut = u; vOut = v;
+    }
+    return ok;
 }
 
 // fragment.glsl:246-307.  Same visiting order and the same accept/cull comparisons as the shader:
@@ -109,59 +115,53 @@ RT_DEV bool triangleTest(const TriRec* __restrict__ rec, f3 o, f3 d, float close
 //    through the stack — it would have been popped immediately;
 //  * an entry already farther than closestT when pushed can never survive its pop (closestT only
 //    shrinks), so it is not pushed; the POPS counter still counts it.
+// Control flow is strictly structured (one loop exit, no continue/return inside): with independent thread
+// scheduling the lanes of a warp reconverge at the immediate post-dominator of each branch, and an early
+// `return` inside the loop moves that point to the function exit — the first version did that and ran with
+// 2 of 32 lanes active (profiles/r01_ncu_notes.md).
 template <bool COUNT>
 RT_DEV RayHit traverse(const DeviceScene& sc, f3 o, f3 d, StackRef st, WorkCount& wc) {
     RayHit best;
     best.t = 1e30f; best.u = 0.f; best.v = 0.f; best.slot = -1;
-    f3 inv = mk3(__frcp_rn(d.x), __frcp_rn(d.y), __frcp_rn(d.z));
+    const f3 inv = mk3(__frcp_rn(d.x), __frcp_rn(d.y), __frcp_rn(d.z));
     uint32_t sp = 0;
     int32_t cur = sc.rootRef;
-    if (cur == RT_REF_NONE) {          // empty scene: the shader's root index fails its bounds check (:259)
-        if (COUNT) wc.pops++;
-        return best;
+    bool running = cur != RT_REF_NONE;   // empty scene: the shader's root index fails its bounds check (:259)
+    if (COUNT) wc.pops++;
+    if (running) {
+        bool hitRoot;
+        const float tRoot = slabTest(o, inv, sc.rootMin[0], sc.rootMin[1], sc.rootMin[2], sc.rootMax[0],
+                                     sc.rootMax[1], sc.rootMax[2], hitRoot);
+        running = hitRoot && !(tRoot > best.t);
     }
-    {
-        float tRoot = slabTest(o, inv, sc.rootMin[0], sc.rootMin[1], sc.rootMin[2], sc.rootMax[0], sc.rootMax[1],
-                               sc.rootMax[2]);
-        if (COUNT) wc.pops++;
-        if (tRoot < 0.0f || tRoot > best.t) return best;
-    }
-    const uint32_t tid = threadIdx.x;
-    for (;;) {
+    uint2* const stack = st.base + threadIdx.x;
+    const uint32_t stride = st.stride;
+    while (running) {
+        bool pop;
         if (cur >= 0) {
-            // internal node: slab-test both children (:281-287)
+            // internal node: slab-test both children (:281-287); an absent child has NaN bounds -> never hit
             const float4* np = reinterpret_cast<const float4*>(sc.nodes + cur);
             const float4 q0 = __ldg(np), q1 = __ldg(np + 1), q2 = __ldg(np + 2);
-            const int4 q3 = __ldg(reinterpret_cast<const int4*>(np + 3));
+            const int2 refs = __ldg(reinterpret_cast<const int2*>(np + 3));
             if (COUNT) wc.internal++;
-            float tA = -1.0f, tB = -1.0f;
-            if (q3.x != RT_REF_NONE) tA = slabTest(o, inv, q0.x, q0.y, q0.z, q0.w, q1.x, q1.y);
-            if (q3.y != RT_REF_NONE) tB = slabTest(o, inv, q1.z, q1.w, q2.x, q2.y, q2.z, q2.w);
-            const bool hitA = tA >= 0.0f, hitB = tB >= 0.0f;
-            int32_t nearRef, farRef; float nearT, farT; bool haveFar = false, haveNear = true;
-            if (hitA && hitB) {
-                const bool aFirst = tA < tB;
-                nearRef = aFirst ? q3.x : q3.y; nearT = aFirst ? tA : tB;
-                farRef = aFirst ? q3.y : q3.x;  farT = aFirst ? tB : tA;
-                haveFar = true;
-                if (COUNT) wc.pops += 2;
-            } else if (hitA) {
-                nearRef = q3.x; nearT = tA; farRef = 0; farT = 0.f;
-                if (COUNT) wc.pops++;
-            } else if (hitB) {
-                nearRef = q3.y; nearT = tB; farRef = 0; farT = 0.f;
-                if (COUNT) wc.pops++;
-            } else {
-                haveNear = false; nearRef = 0; nearT = 0.f; farRef = 0; farT = 0.f;
-            }
-            if (haveFar && !(farT > best.t)) {
-                st.base[sp * st.stride + tid] = make_uint2(uint32_t(farRef), __float_as_uint(farT));
+            bool hitA, hitB;
+            const float tA = slabTest(o, inv, q0.x, q0.y, q0.z, q0.w, q1.x, q1.y, hitA);
+            const float tB = slabTest(o, inv, q1.z, q1.w, q2.x, q2.y, q2.z, q2.w, hitB);
+            if (COUNT) wc.pops += (hitA ? 1u : 0u) + (hitB ? 1u : 0u);
+            const bool aFirst = hitA && (!hitB || tA < tB);     // both hit: A first only if strictly nearer
+            const int32_t nearRef = aFirst ? refs.x : refs.y, farRef = aFirst ? refs.y : refs.x;
+            const float nearT = aFirst ? tA : tB, farT = aFirst ? tB : tA;
+            const bool goNear = (hitA || hitB) && !(nearT > best.t);
+            const bool pushFar = hitA && hitB && !(farT > best.t);
+            if (pushFar) {
+                stack[sp * stride] = make_uint2(uint32_t(farRef), __float_as_uint(farT));
                 sp++;
             }
-            if (haveNear && !(nearT > best.t)) { cur = nearRef; continue; }
+            cur = nearRef;
+            pop = !goNear;
         } else {
             // leaf: every triangle in slot order, first found wins ties (:266-279)
-            uint32_t code = uint32_t(~cur);
+            const uint32_t code = uint32_t(~cur);
             uint32_t count = code & ((1u << RT_LEAF_BITS) - 1u);
             uint32_t first = code >> RT_LEAF_BITS;
             if (count == RT_LEAF_BIG) {
@@ -175,15 +175,17 @@ RT_DEV RayHit traverse(const DeviceScene& sc, f3 o, f3 d, StackRef st, WorkCount
                     best.t = t; best.u = u; best.v = v; best.slot = int32_t(first + k);
                 }
             }
+            pop = true;
         }
-        // pop (:256-262)
-        for (;;) {
-            if (sp == 0) return best;
-            sp--;
-            const uint2 e = st.base[sp * st.stride + tid];
-            if (__uint_as_float(e.y) > best.t) continue;
-            cur = int32_t(e.x);
-            break;
+        if (pop) {
+            // pop until an entry survives the cull against the current closestT (:256-262)
+            running = false;
+            while (sp > 0 && !running) {
+                sp--;
+                const uint2 e = stack[sp * stride];
+                if (!(__uint_as_float(e.y) > best.t)) { cur = int32_t(e.x); running = true; }
+            }
         }
     }
+    return best;
 }

@@ -1,0 +1,15 @@
+"""One render of a named scene for profiling: python tools/prof_case.py <scene> <w> <h> <spp> [variant] [passes]"""
+import os, sys
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+from opengl_raytracer_b200 import configs, rtlib
+from opengl_raytracer_b200.scene import Scene
+name, w, h, spp = sys.argv[1], int(sys.argv[2]), int(sys.argv[3]), int(sys.argv[4])
+variant = sys.argv[5] if len(sys.argv) > 5 else "auto"
+passes = int(sys.argv[6]) if len(sys.argv) > 6 else 2
+cfg = configs.scene_configs()[name].scaled(w, h, spp)
+tris, boxes, idx = Scene(configs.build_objects(cfg.objects)).pack()
+with rtlib.Context(0) as ctx:
+    ctx.set_variant(variant); ctx.scene_upload(tris, boxes, idx); ctx.set_params(cfg.params()); ctx.target_create(w, h)
+    for i in range(passes):
+        ctx.target_clear(); ctx.timer_start(); ctx.render_pass(0, 0, 0); print(name, variant, "ms", ctx.timer_stop())
