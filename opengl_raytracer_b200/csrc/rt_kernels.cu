@@ -7,8 +7,11 @@
 // records come through the read-only path as 16-byte loads; the scene (<= 8 MB) is L2-resident.
 #include <cuda_runtime.h>
 
+#include <algorithm>
+
 #include "../../include/rt_b200.h"
 #include "rt_shade.cuh"
+#include "rt_vote.cuh"
 
 namespace {
 
@@ -121,41 +124,6 @@ __global__ void __launch_bounds__(kBlockThreads) rtPixelKernel(const __grid_cons
     flushCounters<COUNT>(P, pc);
 }
 
-// Variant PERSISTENT: as many CTAs as fit the machine; each warp claims 8x4 pixel tiles from a global
-// counter (one atomic per warp, broadcast by shuffle) until the frame is exhausted.  Removes the tail
-// effect of a fixed pixel->CTA mapping when per-pixel cost varies by orders of magnitude (sky vs mesh).
-template <bool COUNT, bool IDS>
-__global__ void __launch_bounds__(kBlockThreads) rtPersistentKernel(const __grid_constant__ PassParams P) {
-    extern __shared__ uint2 stackMem[];
-    const int lane = threadIdx.x & 31;
-    const int tilesX = (P.ownedW + 7) >> 3, tilesY = (P.ownedH + 3) >> 2;
-    const unsigned int nTiles = (unsigned int)tilesX * (unsigned int)tilesY;
-    PathCounters pc;
-#pragma unroll
-    for (int k = 0; k < RT_CNT_COUNT; k++) pc.v[k] = 0;
-    StackRef st;
-    st.base = stackMem; st.stride = kBlockThreads;
-    for (;;) {
-        unsigned int tile = 0;
-        if (lane == 0) tile = atomicAdd(P.workCounter, 1u);
-        tile = __shfl_sync(0xffffffffu, tile, 0);
-        if (tile >= nTiles) break;
-        const int ox = int(tile % (unsigned int)tilesX) * 8 + (lane & 7);
-        const int oy = int(tile / (unsigned int)tilesX) * 4 + (lane >> 3);
-        if (ox < P.ownedW && oy < P.ownedH) {
-            const int px = ownedToPixel(ox, P.tileSizeX, P.numTilesX, P.tileX);
-            const int py = ownedToPixel(oy, P.tileSizeY, P.numTilesY, P.tileY);
-            int32_t primaryId = -1;
-            const f3 curr = pixelFrame<COUNT, IDS>(P, px, py, st, pc, primaryId);
-            const size_t at = size_t(py) * size_t(P.width) + size_t(px);
-            P.next[at] = accumulate(P, curr, at);
-            if (IDS) P.primaryIds[at] = primaryId;
-        }
-        __syncwarp();
-    }
-    flushCounters<COUNT>(P, pc);
-}
-
 // ---------------------------------------------------------------------------------- utility kernels
 // glReadPixels(GL_RGBA, GL_UNSIGNED_BYTE) of an RGBA32F target (main.py:434): clamp to [0,1], scale by
 // 255, round to nearest.  NaN clamps to 0.
@@ -224,18 +192,21 @@ cudaError_t rtLaunchPixel(const PassParams& P, bool count, bool ids, cudaStream_
 
 cudaError_t rtLaunchPersistent(const PassParams& P, bool count, bool ids, int sms, cudaStream_t stream) {
     if (P.ownedW <= 0 || P.ownedH <= 0) return cudaSuccess;
-    const size_t smem = rtPixelKernelSmem(P.scene.stackDepth);
+    const size_t smem = vote::smemBytes(P.scene.stackDepth);
     cudaError_t e = cudaMemsetAsync(P.workCounter, 0, sizeof(unsigned int), stream);
     if (e != cudaSuccess) return e;
-#define RT_LAUNCH(C, I)                                                                                        \
-    do {                                                                                                       \
-        if (smem > 48 * 1024)                                                                                  \
-            cudaFuncSetAttribute(rtPersistentKernel<C, I>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)); \
-        int perSm = 0;                                                                                         \
-        e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSm, rtPersistentKernel<C, I>, kBlockThreads, smem); \
-        if (e != cudaSuccess) return e;                                                                        \
-        if (perSm < 1) perSm = 1;                                                                              \
-        rtPersistentKernel<C, I><<<sms * perSm, kBlockThreads, smem, stream>>>(P);                            \
+    // no more CTAs than there is work for: one warp per 32 pixel indices
+    const long long tiles = (long long)((P.ownedW + 7) / 8) * ((P.ownedH + 3) / 4);
+    const int needed = int(std::min<long long>((tiles + 3) / 4, 1 << 30));
+#define RT_LAUNCH(C, I)                                                                                          \
+    do {                                                                                                         \
+        if (smem > 48 * 1024)                                                                                    \
+            cudaFuncSetAttribute(vote::rtVoteKernel<C, I>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)); \
+        int perSm = 0;                                                                                           \
+        e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSm, vote::rtVoteKernel<C, I>, vote::kThreads, smem); \
+        if (e != cudaSuccess) return e;                                                                          \
+        if (perSm < 1) perSm = 1;                                                                                \
+        vote::rtVoteKernel<C, I><<<std::min(sms * perSm, std::max(needed, 1)), vote::kThreads, smem, stream>>>(P); \
     } while (0)
     if (count && ids) RT_LAUNCH(true, true);
     else if (count) RT_LAUNCH(true, false);
