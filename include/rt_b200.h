@@ -75,7 +75,9 @@ enum {
     RT_VARIANT_AUTO = 0,
     RT_VARIANT_PIXEL = 1,       /* one thread per pixel, whole pixel-frame in one kernel */
     RT_VARIANT_PERSISTENT = 2,  /* persistent warps fetching pixels with warp-aggregated atomics */
-    RT_VARIANT_WAVEFRONT = 3    /* generate / extend / shade kernels over compacted ray queues */
+    RT_VARIANT_WAVEFRONT = 3,   /* generate / extend / shade kernels over compacted ray queues */
+    RT_VARIANT_POOL = 4         /* persistent CTAs, K rays per lane pooled in shared memory, extend / leaf / shade
+                                   stages picked by warp vote, top of the tree staged in shared memory */
 };
 
 /* flags for rt_render_pass_ex */

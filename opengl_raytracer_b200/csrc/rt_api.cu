@@ -20,6 +20,7 @@
 size_t rtPixelKernelSmem(int stackDepth);
 cudaError_t rtLaunchPixel(const PassParams& P, bool count, bool ids, cudaStream_t stream);
 cudaError_t rtLaunchPersistent(const PassParams& P, bool count, bool ids, int sms, cudaStream_t stream);
+cudaError_t rtLaunchPool(const PassParams& P, bool count, bool ids, int sms, cudaStream_t stream);
 cudaError_t rtLaunchToRgba8(const float4* src, uchar4* dst, size_t n, cudaStream_t stream);
 cudaError_t rtLaunchBandCopy(float4* target, float4* dense, int width, int rows, int tileSizeY, int numTilesY,
                              int tile, int toDense, cudaStream_t stream);
@@ -362,7 +363,7 @@ int rt_set_params(rt_ctx* c, const rt_params* p) {
 
 int rt_set_variant(rt_ctx* c, int variant) {
     if (!c) return RT_ERR_INVALID;
-    if (variant < RT_VARIANT_AUTO || variant > RT_VARIANT_WAVEFRONT) return fail(c, RT_ERR_INVALID, "unknown variant %d", variant);
+    if (variant < RT_VARIANT_AUTO || variant > RT_VARIANT_POOL) return fail(c, RT_ERR_INVALID, "unknown variant %d", variant);
     c->variant = variant;
     return RT_OK;
 }
@@ -441,7 +442,9 @@ int renderPass(rt_ctx* c, int frameNumber, int tileX, int tileY, int flags, int 
                                    cudaMemcpyDeviceToDevice, c->stream));
     }
     cudaError_t e;
-    if (c->variant == RT_VARIANT_PERSISTENT)
+    if (c->variant == RT_VARIANT_POOL)
+        e = rtLaunchPool(P, P.counters != nullptr, P.primaryIds != nullptr, c->smCount, c->stream);
+    else if (c->variant == RT_VARIANT_PERSISTENT)
         e = rtLaunchPersistent(P, P.counters != nullptr, P.primaryIds != nullptr, c->smCount, c->stream);
     else
         e = rtLaunchPixel(P, P.counters != nullptr, P.primaryIds != nullptr, c->stream);

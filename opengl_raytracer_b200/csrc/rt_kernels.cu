@@ -8,10 +8,12 @@
 #include <cuda_runtime.h>
 
 #include <algorithm>
+#include <cstdlib>
 
 #include "../../include/rt_b200.h"
 #include "rt_shade.cuh"
 #include "rt_vote.cuh"
+#include "rt_pool.cuh"
 
 namespace {
 
@@ -190,14 +192,20 @@ cudaError_t rtLaunchPixel(const PassParams& P, bool count, bool ids, cudaStream_
     return cudaGetLastError();
 }
 
-cudaError_t rtLaunchPersistent(const PassParams& P, bool count, bool ids, int sms, cudaStream_t stream) {
+cudaError_t rtLaunchPersistent(const PassParams& Pin, bool count, bool ids, int sms, cudaStream_t stream) {
+    PassParams P = Pin;
     if (P.ownedW <= 0 || P.ownedH <= 0) return cudaSuccess;
-    const size_t smem = vote::smemBytes(P.scene.stackDepth);
+    const size_t base = vote::smemBytes(P.scene.stackDepth);
+    const size_t budget = 200 * 1024;
+    long long top = base < budget ? (long long)((budget - base) / 64) : 0;
+    if (const char* e = getenv("RT_TOP_NODES")) top = std::min<long long>(top, atoll(e));
+    P.topCount = int(std::min<long long>(top, P.scene.nNodes));
+    const size_t smem = base + vote::topBytes(P.topCount);
     cudaError_t e = cudaMemsetAsync(P.workCounter, 0, sizeof(unsigned int), stream);
     if (e != cudaSuccess) return e;
     // no more CTAs than there is work for: one warp per 32 pixel indices
     const long long tiles = (long long)((P.ownedW + 7) / 8) * ((P.ownedH + 3) / 4);
-    const int needed = int(std::min<long long>((tiles + 3) / 4, 1 << 30));
+    const int needed = int(std::min<long long>((tiles * 32 + vote::kThreads - 1) / vote::kThreads, 1 << 30));
 #define RT_LAUNCH(C, I)                                                                                          \
     do {                                                                                                         \
         if (smem > 48 * 1024)                                                                                    \
@@ -214,6 +222,56 @@ cudaError_t rtLaunchPersistent(const PassParams& P, bool count, bool ids, int sm
     else RT_LAUNCH(false, false);
 #undef RT_LAUNCH
     return cudaGetLastError();
+}
+
+// ---- POOL variant: one persistent CTA per SM; shared memory = ray pool + the top of the tree
+namespace {
+template <int T, int K, int S>
+cudaError_t launchPoolCfg(PassParams P, bool count, bool ids, int sms, int topWanted, cudaStream_t stream) {
+    int dev = 0, maxSmem = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&maxSmem, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev);
+    const size_t slots = pool::Smem<T, K>::slotBytes(P.scene.stackDepth);
+    if (slots + 1024 > size_t(maxSmem)) return cudaErrorInvalidConfiguration;
+    long long top = (long long)((size_t(maxSmem) - slots - 512) / 56);
+    if (topWanted >= 0) top = std::min<long long>(top, topWanted);
+    P.topCount = int(std::min<long long>(top, P.scene.nNodes));
+    const size_t smem = pool::Smem<T, K>::bytes(P.scene.stackDepth, P.topCount);
+    const long long tiles = (long long)((P.ownedW + 7) / 8) * ((P.ownedH + 3) / 4);
+    const int needed = int(std::min<long long>((tiles * 32 + T * K - 1) / (T * K), 1 << 30));
+    const int grid = std::min(sms, std::max(needed, 1));
+    cudaError_t e = cudaSuccess;
+#define RT_LAUNCH(C, I)                                                                                        \
+    do {                                                                                                       \
+        e = cudaFuncSetAttribute(pool::rtPoolKernel<T, K, S, C, I>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)); \
+        if (e != cudaSuccess) return e;                                                                        \
+        pool::rtPoolKernel<T, K, S, C, I><<<grid, T, smem, stream>>>(P);                                       \
+    } while (0)
+    if (count && ids) RT_LAUNCH(true, true);
+    else if (count) RT_LAUNCH(true, false);
+    else if (ids) RT_LAUNCH(false, true);
+    else RT_LAUNCH(false, false);
+#undef RT_LAUNCH
+    return cudaGetLastError();
+}
+}  // namespace
+
+cudaError_t rtLaunchPool(const PassParams& P, bool count, bool ids, int sms, cudaStream_t stream) {
+    if (P.ownedW <= 0 || P.ownedH <= 0) return cudaSuccess;
+    cudaError_t e = cudaMemsetAsync(P.workCounter, 0, sizeof(unsigned int), stream);
+    if (e != cudaSuccess) return e;
+    // tuning knobs (measurement only; the defaults are what profiles/ documents)
+    int cfg = 0, top = 1024;
+    if (const char* v = getenv("RT_POOL_CFG")) cfg = atoi(v);
+    if (const char* v = getenv("RT_TOP_NODES")) top = atoi(v);
+    switch (cfg) {
+        case 1: return launchPoolCfg<256, 2, 4>(P, count, ids, sms, top, stream);
+        case 2: return launchPoolCfg<256, 3, 4>(P, count, ids, sms, top, stream);
+        case 3: return launchPoolCfg<384, 2, 2>(P, count, ids, sms, top, stream);
+        case 4: return launchPoolCfg<384, 2, 8>(P, count, ids, sms, top, stream);
+        case 5: return launchPoolCfg<512, 1, 4>(P, count, ids, sms, top, stream);
+        default: return launchPoolCfg<384, 2, 4>(P, count, ids, sms, top, stream);
+    }
 }
 
 cudaError_t rtLaunchToRgba8(const float4* src, uchar4* dst, size_t n, cudaStream_t stream) {

@@ -80,4 +80,5 @@ struct PassParams {
     int32_t ownedW, ownedH;
     int32_t sumMode;                // 1: next = prev + curr (frame-sharded progressive mode), 0: running mean
     unsigned int* workCounter;      // persistent variant
+    int32_t topCount;               // persistent variant: nodes [0, topCount) are staged in shared memory
 };

@@ -20,13 +20,19 @@
 
 namespace vote {
 
-constexpr int kThreads = 128;
+#ifndef RT_VOTE_THREADS
+#define RT_VOTE_THREADS 512
+#endif
+constexpr int kThreads = RT_VOTE_THREADS;
 constexpr int kScratchWords = 7;          // per lane: primary direction (3) + primary hit (slot, t, u, v)
 constexpr int MODE_INTERNAL = 0, MODE_LEAF = 1, MODE_SHADE = 2, MODE_DONE = 3;
 
 inline size_t smemBytes(int stackDepth) {
     return size_t(stackDepth) * kThreads * sizeof(uint2) + size_t(kScratchWords) * kThreads * sizeof(uint32_t);
 }
+// Top of the tree in shared memory (nodes are numbered breadth-first, so "the first topCount nodes" are the top
+// levels): four float4 arrays (q0 | q1 | q2 | refs) so that lanes reading record `cur` spread over all bank groups.
+inline size_t topBytes(int topCount) { return size_t(topCount) * 64; }
 
 struct Lane {
     // traversal
@@ -75,10 +81,19 @@ RT_DEV void popNext(Lane& L, const uint2* stack, uint32_t stride) {
 
 // One internal-node step (fragment.glsl:281-304), see traverse() for the order-preserving details.
 template <bool COUNT>
-RT_DEV void stepInternal(const DeviceScene& sc, Lane& L, uint2* stack, uint32_t stride, uint32_t* cnt) {
-    const float4* np = reinterpret_cast<const float4*>(sc.nodes + L.cur);
-    const float4 q0 = __ldg(np), q1 = __ldg(np + 1), q2 = __ldg(np + 2);
-    const int2 refs = __ldg(reinterpret_cast<const int2*>(np + 3));
+RT_DEV void stepInternal(const DeviceScene& sc, Lane& L, uint2* stack, uint32_t stride, uint32_t* cnt,
+                         const float4* top, int topCount) {
+    float4 q0, q1, q2;
+    int2 refs;
+    if (L.cur < topCount) {
+        q0 = top[L.cur]; q1 = top[topCount + L.cur]; q2 = top[2 * topCount + L.cur];
+        const float4 r = top[3 * topCount + L.cur];
+        refs = make_int2(__float_as_int(r.x), __float_as_int(r.y));
+    } else {
+        const float4* np = reinterpret_cast<const float4*>(sc.nodes + L.cur);
+        q0 = __ldg(np); q1 = __ldg(np + 1); q2 = __ldg(np + 2);
+        refs = __ldg(reinterpret_cast<const int2*>(np + 3));
+    }
     bool hitA, hitB;
     const float tA = slabTest(L.o, L.inv, q0.x, q0.y, q0.z, q0.w, q1.x, q1.y, hitA);
     const float tB = slabTest(L.o, L.inv, q1.z, q1.w, q2.x, q2.y, q2.z, q2.w, hitB);
@@ -138,6 +153,14 @@ __global__ void __launch_bounds__(kThreads) rtVoteKernel(const __grid_constant__
     uint2* const stack = smem + threadIdx.x;
     const uint32_t stride = kThreads;
     uint32_t* const scratch = reinterpret_cast<uint32_t*>(smem + size_t(sc.stackDepth) * kThreads) + threadIdx.x;
+    float4* const top = reinterpret_cast<float4*>(reinterpret_cast<uint32_t*>(smem + size_t(sc.stackDepth) * kThreads) +
+                                                  size_t(kScratchWords) * kThreads);
+    const int topCount = P.topCount;
+    for (int i = threadIdx.x; i < topCount * 4; i += kThreads) {
+        const int node = i >> 2, part = i & 3;
+        top[part * topCount + node] = __ldg(reinterpret_cast<const float4*>(sc.nodes + node) + part);
+    }
+    __syncthreads();
 
     const int tilesX = (P.ownedW + 7) >> 3, tilesY = (P.ownedH + 3) >> 2;
     const unsigned int totalIdx = (unsigned int)tilesX * (unsigned int)tilesY * 32u;
@@ -301,7 +324,7 @@ __global__ void __launch_bounds__(kThreads) rtVoteKernel(const __grid_constant__
             if (L.mode == MODE_LEAF) stepLeaf<COUNT>(sc, L, stack, stride, cnt);
         } else {
             // --------------------------------------------------------------- INTERNAL section
-            if (L.mode == MODE_INTERNAL) stepInternal<COUNT>(sc, L, stack, stride, cnt);
+            if (L.mode == MODE_INTERNAL) stepInternal<COUNT>(sc, L, stack, stride, cnt, top, topCount);
         }
     }
 

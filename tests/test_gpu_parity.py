@@ -9,7 +9,7 @@ from opengl_raytracer_b200 import rtlib
 
 pytestmark = pytest.mark.gpu
 
-VARIANTS = ["pixel", "persistent"]
+VARIANTS = ["pixel", "persistent", "pool"]
 EXACT_COUNTERS = ("rays", "internal", "leaves", "tri_tests", "hits", "pops", "paths")
 
 
