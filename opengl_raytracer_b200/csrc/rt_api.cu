@@ -21,6 +21,7 @@ size_t rtPixelKernelSmem(int stackDepth);
 cudaError_t rtLaunchPixel(const PassParams& P, bool count, bool ids, cudaStream_t stream);
 cudaError_t rtLaunchPersistent(const PassParams& P, bool count, bool ids, int sms, cudaStream_t stream);
 cudaError_t rtLaunchPool(const PassParams& P, bool count, bool ids, int sms, cudaStream_t stream);
+cudaError_t rtLaunchWavefront(const PassParams& P, bool count, bool ids, int sms, cudaStream_t stream);
 cudaError_t rtLaunchToRgba8(const float4* src, uchar4* dst, size_t n, cudaStream_t stream);
 cudaError_t rtLaunchBandCopy(float4* target, float4* dense, int width, int rows, int tileSizeY, int numTilesY,
                              int tile, int toDense, cudaStream_t stream);
@@ -52,6 +53,13 @@ struct rt_ctx {
     uchar4* dRgba8 = nullptr;
     unsigned long long* dCounters = nullptr;
     unsigned int* dWork = nullptr;
+    // wavefront variant: queue of pixels whose primary ray hit (allocated on first use, sized to the target)
+    float4* dQueueA = nullptr;
+    float4* dQueueB = nullptr;
+    uint32_t* dQueuePix = nullptr;
+    uint4* dQueueWork = nullptr;
+    unsigned int* dQueueCount = nullptr;
+    size_t queueCapacity = 0;
 };
 
 namespace {
@@ -103,7 +111,30 @@ void freeScene(rt_ctx* c) {
     c->scene = DeviceScene{};
 }
 
+void freeQueue(rt_ctx* c) {
+    cudaFree(c->dQueueA); cudaFree(c->dQueueB); cudaFree(c->dQueuePix); cudaFree(c->dQueueWork);
+    c->dQueueA = c->dQueueB = nullptr; c->dQueuePix = nullptr; c->dQueueWork = nullptr;
+    c->queueCapacity = 0;
+}
+
+// The queue can hold every pixel of the target (all primary rays may hit); the work array only exists once a
+// counting pass asked for it.
+cudaError_t ensureQueue(rt_ctx* c, bool withWork) {
+    const size_t n = size_t(c->width) * c->height;
+    cudaError_t e = cudaSuccess;
+    if (c->queueCapacity < n) {
+        freeQueue(c);
+        if ((e = cudaMalloc(&c->dQueueA, n * sizeof(float4))) != cudaSuccess) return e;
+        if ((e = cudaMalloc(&c->dQueueB, n * sizeof(float4))) != cudaSuccess) return e;
+        if ((e = cudaMalloc(&c->dQueuePix, n * sizeof(uint32_t))) != cudaSuccess) return e;
+        c->queueCapacity = n;
+    }
+    if (withWork && !c->dQueueWork) e = cudaMalloc(&c->dQueueWork, c->queueCapacity * sizeof(uint4));
+    return e;
+}
+
 void freeTargets(rt_ctx* c) {
+    freeQueue(c);
     cudaFree(c->target[0]); cudaFree(c->target[1]); cudaFree(c->dIds); cudaFree(c->dRgba8);
     c->target[0] = c->target[1] = nullptr; c->dIds = nullptr; c->dRgba8 = nullptr;
     c->width = c->height = 0;
@@ -143,7 +174,8 @@ int rt_create(rt_ctx** out, int device) {
     if (cudaStreamCreateWithFlags(&c->ownStream, cudaStreamNonBlocking) != cudaSuccess ||
         cudaEventCreate(&c->ev0) != cudaSuccess || cudaEventCreate(&c->ev1) != cudaSuccess ||
         cudaMalloc(&c->dCounters, RT_CNT_COUNT * sizeof(unsigned long long)) != cudaSuccess ||
-        cudaMalloc(&c->dWork, sizeof(unsigned int)) != cudaSuccess) {
+        cudaMalloc(&c->dWork, sizeof(unsigned int)) != cudaSuccess ||
+        cudaMalloc(&c->dQueueCount, sizeof(unsigned int)) != cudaSuccess) {
         delete c;
         return RT_ERR_CUDA;
     }
@@ -159,7 +191,7 @@ void rt_destroy(rt_ctx* c) {
     cudaStreamSynchronize(c->stream);
     freeScene(c);
     freeTargets(c);
-    cudaFree(c->dCounters); cudaFree(c->dWork);
+    cudaFree(c->dCounters); cudaFree(c->dWork); cudaFree(c->dQueueCount);
     if (c->ev0) cudaEventDestroy(c->ev0);
     if (c->ev1) cudaEventDestroy(c->ev1);
     if (c->ownStream) cudaStreamDestroy(c->ownStream);
@@ -442,9 +474,21 @@ int renderPass(rt_ctx* c, int frameNumber, int tileX, int tileY, int flags, int 
                                    cudaMemcpyDeviceToDevice, c->stream));
     }
     cudaError_t e;
-    if (c->variant == RT_VARIANT_POOL)
+    int variant = c->variant;
+    // AUTO, by measurement on B200 (profiles/r01_variants.md): many samples per pixel make the per-pixel work
+    // uneven (sky pixels finish at once, surface pixels run rays_per_pixel paths) and the persistent warp-vote
+    // kernel wins; otherwise the one-thread-per-pixel kernel does
+    if (variant == RT_VARIANT_AUTO) variant = u.rays_per_pixel >= 16 ? RT_VARIANT_PERSISTENT : RT_VARIANT_PIXEL;
+    if (variant == RT_VARIANT_WAVEFRONT && (c->width > 65535 || c->height > 65535)) variant = RT_VARIANT_PIXEL;
+    if (variant == RT_VARIANT_WAVEFRONT) {
+        e = ensureQueue(c, P.counters != nullptr);
+        if (e != cudaSuccess) return fail(c, RT_ERR_NOMEM, "wavefront queue: %s", cudaGetErrorString(e));
+        P.queueA = c->dQueueA; P.queueB = c->dQueueB; P.queuePix = c->dQueuePix; P.queueWork = c->dQueueWork;
+        P.queueCount = c->dQueueCount;
+        e = rtLaunchWavefront(P, P.counters != nullptr, P.primaryIds != nullptr, c->smCount, c->stream);
+    } else if (variant == RT_VARIANT_POOL)
         e = rtLaunchPool(P, P.counters != nullptr, P.primaryIds != nullptr, c->smCount, c->stream);
-    else if (c->variant == RT_VARIANT_PERSISTENT)
+    else if (variant == RT_VARIANT_PERSISTENT)
         e = rtLaunchPersistent(P, P.counters != nullptr, P.primaryIds != nullptr, c->smCount, c->stream);
     else
         e = rtLaunchPixel(P, P.counters != nullptr, P.primaryIds != nullptr, c->stream);

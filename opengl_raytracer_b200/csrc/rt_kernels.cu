@@ -14,6 +14,7 @@
 #include "rt_shade.cuh"
 #include "rt_vote.cuh"
 #include "rt_pool.cuh"
+#include "rt_wave.cuh"
 
 namespace {
 
@@ -196,9 +197,9 @@ cudaError_t rtLaunchPersistent(const PassParams& Pin, bool count, bool ids, int 
     PassParams P = Pin;
     if (P.ownedW <= 0 || P.ownedH <= 0) return cudaSuccess;
     const size_t base = vote::smemBytes(P.scene.stackDepth);
-    const size_t budget = 200 * 1024;
-    long long top = base < budget ? (long long)((budget - base) / 64) : 0;
-    if (const char* e = getenv("RT_TOP_NODES")) top = std::min<long long>(top, atoll(e));
+    // optional staging of the tree top in shared memory (measured: no gain at this CTA size; off by default)
+    long long top = 0;
+    if (const char* e = getenv("RT_VOTE_TOP_NODES")) top = std::min<long long>(atoll(e), (long long)((96 * 1024 - base) / 64));
     P.topCount = int(std::min<long long>(top, P.scene.nNodes));
     const size_t smem = base + vote::topBytes(P.topCount);
     cudaError_t e = cudaMemsetAsync(P.workCounter, 0, sizeof(unsigned int), stream);
@@ -258,6 +259,7 @@ cudaError_t launchPoolCfg(PassParams P, bool count, bool ids, int sms, int topWa
 
 cudaError_t rtLaunchPool(const PassParams& P, bool count, bool ids, int sms, cudaStream_t stream) {
     if (P.ownedW <= 0 || P.ownedH <= 0) return cudaSuccess;
+    if (P.scene.stackDepth > pool::kMaxDepth) return rtLaunchPixel(P, count, ids, stream);   // very deep (degenerate) trees
     cudaError_t e = cudaMemsetAsync(P.workCounter, 0, sizeof(unsigned int), stream);
     if (e != cudaSuccess) return e;
     // tuning knobs (measurement only; the defaults are what profiles/ documents)
@@ -272,6 +274,48 @@ cudaError_t rtLaunchPool(const PassParams& P, bool count, bool ids, int sms, cud
         case 5: return launchPoolCfg<512, 1, 4>(P, count, ids, sms, top, stream);
         default: return launchPoolCfg<384, 2, 4>(P, count, ids, sms, top, stream);
     }
+}
+
+// ---- WAVEFRONT variant: primary stage (one thread per owned pixel) -> queue -> path stage (persistent warps)
+cudaError_t rtLaunchWavefront(const PassParams& P, bool count, bool ids, int sms, cudaStream_t stream) {
+    if (P.ownedW <= 0 || P.ownedH <= 0) return cudaSuccess;
+    cudaError_t e = cudaMemsetAsync(P.workCounter, 0, sizeof(unsigned int), stream);
+    if (e != cudaSuccess) return e;
+    e = cudaMemsetAsync(P.queueCount, 0, sizeof(unsigned int), stream);
+    if (e != cudaSuccess) return e;
+    const size_t smem = wave::smemBytes(P.scene.stackDepth);
+    dim3 grid((P.ownedW + 15) / 16, (P.ownedH + 7) / 8);
+#define RT_LAUNCH1(C, I)                                                                                       \
+    do {                                                                                                       \
+        if (smem > 48 * 1024)                                                                                  \
+            cudaFuncSetAttribute(wave::rtPrimaryKernel<C, I>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)); \
+        wave::rtPrimaryKernel<C, I><<<grid, wave::kThreads, smem, stream>>>(P);                                \
+    } while (0)
+    if (count && ids) RT_LAUNCH1(true, true);
+    else if (count) RT_LAUNCH1(true, false);
+    else if (ids) RT_LAUNCH1(false, true);
+    else RT_LAUNCH1(false, false);
+#undef RT_LAUNCH1
+    e = cudaGetLastError();
+    if (e != cudaSuccess) return e;
+    if (P.nBounces <= 0 || P.raysPerPixel <= 0) return cudaSuccess;   // nothing was queued
+    const long long pixels = (long long)P.ownedW * P.ownedH;
+#define RT_LAUNCH2(C)                                                                                          \
+    do {                                                                                                       \
+        if (smem > 48 * 1024)                                                                                  \
+            cudaFuncSetAttribute(wave::rtPathKernel<C>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)); \
+        int perSm = 0;                                                                                         \
+        e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSm, wave::rtPathKernel<C>, wave::kThreads, smem); \
+        if (e != cudaSuccess) return e;                                                                        \
+        if (perSm < 1) perSm = 1;                                                                              \
+        const long long want = (pixels + wave::kThreads - 1) / wave::kThreads;                                 \
+        wave::rtPathKernel<C><<<int(std::min<long long>((long long)sms * perSm, std::max<long long>(want, 1))), \
+                                wave::kThreads, smem, stream>>>(P);                                            \
+    } while (0)
+    if (count) RT_LAUNCH2(true);
+    else RT_LAUNCH2(false);
+#undef RT_LAUNCH2
+    return cudaGetLastError();
 }
 
 cudaError_t rtLaunchToRgba8(const float4* src, uchar4* dst, size_t n, cudaStream_t stream) {

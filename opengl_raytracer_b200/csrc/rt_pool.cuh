@@ -28,7 +28,10 @@
 
 namespace pool {
 
-constexpr int MODE_INTERNAL = 0, MODE_LEAF = 1, MODE_SHADE = 2, MODE_DONE = 3;
+// A slot's mode.  INTERNAL: at a node whose record is staged in shared memory; DEEP: at a node that must come
+// from global memory (index >= topCount), or about to re-pop after a culled pop (cur == RT_REF_NONE).
+constexpr int MODE_INTERNAL = 0, MODE_LEAF = 1, MODE_SHADE = 2, MODE_DONE = 3, MODE_DEEP = 4;
+constexpr int kMaxDepth = 31;   // sp is kept in 5 bits
 constexpr uint32_t FULL = 0xffffffffu;
 
 // Stage thresholds (lanes of the warp that have a ray waiting for the stage).
@@ -37,6 +40,9 @@ constexpr uint32_t FULL = 0xffffffffu;
 #endif
 #ifndef RT_POOL_TS
 #define RT_POOL_TS 12
+#endif
+#ifndef RT_POOL_TD
+#define RT_POOL_TD 12
 #endif
 
 // Per-pixel path state of a slot.  Lives in local memory (indexed by the slot number at run time); it is only
@@ -79,11 +85,15 @@ struct Smem {
     }
 };
 
-RT_DEV int modeOf(uint32_t modes, int k) { return int((modes >> (8 * k)) & 3u); }
-RT_DEV uint32_t spOf(uint32_t modes, int k) { return (modes >> (8 * k + 2)) & 63u; }
+RT_DEV int modeOf(uint32_t modes, int k) { return int((modes >> (8 * k)) & 7u); }
+RT_DEV uint32_t spOf(uint32_t modes, int k) { return (modes >> (8 * k + 3)) & 31u; }
 RT_DEV uint32_t withSlot(uint32_t modes, int k, int mode, uint32_t sp) {
-    return (modes & ~(0xffu << (8 * k))) | ((uint32_t(mode) | (sp << 2)) << (8 * k));
+    return (modes & ~(0xffu << (8 * k))) | ((uint32_t(mode) | (sp << 3)) << (8 * k));
 }
+RT_DEV int classify(int32_t cur, int topCount) {
+    return cur < 0 ? MODE_LEAF : (cur >= topCount ? MODE_DEEP : MODE_INTERNAL);
+}
+RT_DEV void prefetchL1(const void* p) { asm volatile("prefetch.global.L1 [%0];" ::"l"(p)); }
 // lowest slot in `mode`, or -1
 template <int K>
 RT_DEV int firstIn(uint32_t modes, int mode) {
@@ -95,19 +105,43 @@ RT_DEV int firstIn(uint32_t modes, int mode) {
 }
 
 // Pop until an entry survives the cull against the current closestT (fragment.glsl:256-262).
-RT_DEV void popNext(const uint2* stack, uint32_t stride, float bestT, uint32_t& sp, int32_t& cur, int& mode) {
+RT_DEV void popNext(const uint2* stack, uint32_t stride, float bestT, uint32_t& sp, int32_t& cur, int& mode, int topCount) {
     bool found = false;
     while (sp > 0 && !found) {
         sp--;
         const uint2 e = stack[sp * stride];
         if (!(__uint_as_float(e.y) > bestT)) { cur = int32_t(e.x); found = true; }
     }
-    mode = found ? (cur >= 0 ? MODE_INTERNAL : MODE_LEAF) : MODE_SHADE;
+    mode = found ? classify(cur, topCount) : MODE_SHADE;
+}
+
+// The arithmetic of one internal-node step (fragment.glsl:281-304) on a fetched record; see traverse() in
+// rt_device.cuh for why this preserves the shader's visiting order.
+struct StepOut {
+    bool goNear, pushFar;
+    int32_t nearRef, farRef;
+    float farT;
+    uint32_t hits;
+};
+RT_DEV StepOut nodeMath(f3 o, f3 inv, float bestT, float4 q0, float4 q1, float4 q2, int2 refs) {
+    bool hitA, hitB;
+    const float tA = slabTest(o, inv, q0.x, q0.y, q0.z, q0.w, q1.x, q1.y, hitA);
+    const float tB = slabTest(o, inv, q1.z, q1.w, q2.x, q2.y, q2.z, q2.w, hitB);
+    const bool aFirst = hitA && (!hitB || tA < tB);
+    StepOut r;
+    r.nearRef = aFirst ? refs.x : refs.y;
+    r.farRef = aFirst ? refs.y : refs.x;
+    const float nearT = aFirst ? tA : tB;
+    r.farT = aFirst ? tB : tA;
+    r.goNear = (hitA || hitB) && !(nearT > bestT);
+    r.pushFar = hitA && hitB && !(r.farT > bestT);
+    r.hits = (hitA ? 1u : 0u) + (hitB ? 1u : 0u);
+    return r;
 }
 
 // Start the traversal of (o, d) in slot si: root slab test (fragment.glsl:253-262).  Returns the slot's mode.
 template <bool COUNT, int T, int K>
-RT_DEV int beginRay(const DeviceScene& sc, const Smem<T, K>& sm, int si, f3 o, f3 d, uint32_t* cnt, PathState& s) {
+RT_DEV int beginRay(const DeviceScene& sc, const Smem<T, K>& sm, int si, f3 o, f3 d, uint32_t* cnt, PathState& s, int topCount) {
     const f3 inv = mk3(__frcp_rn(d.x), __frcp_rn(d.y), __frcp_rn(d.z));
     sm.A[si] = make_float4(o.x, o.y, o.z, 1e30f);
     sm.B[si] = make_float4(inv.x, inv.y, inv.z, 0.f);
@@ -124,7 +158,7 @@ RT_DEV int beginRay(const DeviceScene& sc, const Smem<T, K>& sm, int si, f3 o, f
                                      sc.rootMax[1], sc.rootMax[2], hitRoot);
         running = hitRoot && !(tRoot > 1e30f);
     }
-    return running ? (sc.rootRef >= 0 ? MODE_INTERNAL : MODE_LEAF) : MODE_SHADE;
+    return running ? classify(sc.rootRef, topCount) : MODE_SHADE;
 }
 
 template <int T, int K, int S, bool COUNT, bool IDS>
@@ -166,24 +200,27 @@ __global__ void __launch_bounds__(T, 1) rtPoolKernel(const __grid_constant__ Pas
 
     for (;;) {
         const int kI = firstIn<K>(modes, MODE_INTERNAL);
+        const int kD = firstIn<K>(modes, MODE_DEEP);
         const int kL = firstIn<K>(modes, MODE_LEAF);
         const int kS = firstIn<K>(modes, MODE_SHADE);
         const uint32_t mI = __ballot_sync(FULL, kI >= 0);
+        const uint32_t mD = __ballot_sync(FULL, kD >= 0);
         const uint32_t mL = __ballot_sync(FULL, kL >= 0);
         const uint32_t mS = __ballot_sync(FULL, kS >= 0);
-        if ((mI | mL | mS) == 0u) break;
+        if ((mI | mD | mL | mS) == 0u) break;
 
-        // stage choice (warp-uniform): the rare, expensive stages run when enough lanes wait for them, the hot
-        // EXTEND stage otherwise; when nothing can extend, whichever of the other two has more lanes
-        const int nI = __popc(mI), nL = __popc(mL), nS = __popc(mS);
+        // stage choice (warp-uniform): the rarer, slower stages run when enough lanes wait for them, the hot
+        // EXTEND stage otherwise; when nothing can extend, whichever of the others has most lanes
+        const int nI = __popc(mI), nD = __popc(mD), nL = __popc(mL), nS = __popc(mS);
         int stage;
         if (nS >= RT_POOL_TS) stage = MODE_SHADE;
         else if (nL >= RT_POOL_TL) stage = MODE_LEAF;
+        else if (nD >= RT_POOL_TD) stage = MODE_DEEP;
         else if (nI > 0) stage = MODE_INTERNAL;
-        else stage = nL >= nS ? MODE_LEAF : MODE_SHADE;
+        else stage = (nL >= nS && nL >= nD) ? MODE_LEAF : (nD >= nS ? MODE_DEEP : MODE_SHADE);
 
         if (stage == MODE_INTERNAL) {
-            // ------------------------------------------------------------------------ EXTEND stage
+            // --------------------------------------------------- EXTEND stage: node records from shared memory only
             if (kI >= 0) {
                 const int si = kI * T + tid;
                 const float4 a = sm.A[si], b = sm.B[si];
@@ -197,58 +234,71 @@ __global__ void __launch_bounds__(T, 1) rtPoolKernel(const __grid_constant__ Pas
 #pragma unroll 1
                 for (int s = 0; s < S; s++) {
                     if (mode == MODE_INTERNAL) {
-                        // one internal-node step (fragment.glsl:281-304), see traverse() for the order-preserving
-                        // details.  cur == RT_REF_NONE marks "the last pop was culled, pop again" (no node this step).
-                        bool goNear = false;
-                        int32_t nearRef = 0;
-                        if (cur != RT_REF_NONE) {
-                            float4 q0, q1, q2;
-                            int2 refs;
-                            if (cur < topCount) {
-                                q0 = sm.top[cur]; q1 = sm.top[topCount + cur]; q2 = sm.top[2 * topCount + cur];
-                                refs = sm.topRefs[cur];
-                            } else {
-                                const float4* np = reinterpret_cast<const float4*>(sc.nodes + cur);
-                                q0 = __ldg(np); q1 = __ldg(np + 1); q2 = __ldg(np + 2);
-                                refs = __ldg(reinterpret_cast<const int2*>(np + 3));
-                            }
-                            bool hitA, hitB;
-                            const float tA = slabTest(o, inv, q0.x, q0.y, q0.z, q0.w, q1.x, q1.y, hitA);
-                            const float tB = slabTest(o, inv, q1.z, q1.w, q2.x, q2.y, q2.z, q2.w, hitB);
-                            if (COUNT) { wInternal++; wPops += (hitA ? 1u : 0u) + (hitB ? 1u : 0u); }
-                            const bool aFirst = hitA && (!hitB || tA < tB);
-                            nearRef = aFirst ? refs.x : refs.y;
-                            const int32_t farRef = aFirst ? refs.y : refs.x;
-                            const float nearT = aFirst ? tA : tB, farT = aFirst ? tB : tA;
-                            goNear = (hitA || hitB) && !(nearT > bestT);
-                            const bool pushFar = hitA && hitB && !(farT > bestT);
-                            if (pushFar) {
-                                stack[sp * STRIDE] = make_uint2(uint32_t(farRef), __float_as_uint(farT));
-                                sp++;
-                            }
+                        const StepOut r = nodeMath(o, inv, bestT, sm.top[cur], sm.top[topCount + cur],
+                                                   sm.top[2 * topCount + cur], sm.topRefs[cur]);
+                        if (COUNT) { wInternal++; wPops += r.hits; }
+                        if (r.pushFar) {
+                            stack[sp * STRIDE] = make_uint2(uint32_t(r.farRef), __float_as_uint(r.farT));
+                            sp++;
                         }
-                        // next node: the near child, else ONE pop (fragment.glsl:256-262) — no loop here: inside a
-                        // burst closestT is constant, so a popped entry is culled only if a leaf improved closestT
-                        // after it was pushed; such a lane simply pops again on its next step
-                        const bool havePop = !goNear && sp > 0;
-                        uint2 e = make_uint2(0u, 0u);
-                        if (havePop) e = stack[(sp - 1) * STRIDE];
-                        if (goNear) {
-                            cur = nearRef;
-                        } else if (havePop) {
-                            sp--;
-                            cur = !(__uint_as_float(e.y) > bestT) ? int32_t(e.x) : RT_REF_NONE;
-                        } else {
-                            mode = MODE_SHADE;
-                        }
-                        if (mode != MODE_SHADE && cur < 0) mode = MODE_LEAF;
+                        // next node: the near child, else ONE pop (fragment.glsl:256-262).  closestT is constant inside
+                        // a burst, so a popped entry is culled only if a leaf improved closestT after it was pushed; the
+                        // rare culled pop parks the slot in DEEP mode (cur = RT_REF_NONE), whose stage pops in a loop.
+                        const bool havePop = !r.goNear && sp > 0;
+                        uint2 e = make_uint2(uint32_t(RT_REF_NONE), 0u);
+                        if (havePop) { sp--; e = stack[sp * STRIDE]; }
+                        const bool culled = __uint_as_float(e.y) > bestT;
+                        cur = r.goNear ? r.nearRef : (culled ? RT_REF_NONE : int32_t(e.x));
+                        mode = (r.goNear || havePop) ? classify(cur, topCount) : MODE_SHADE;
                     }
                 }
+                if (mode == MODE_DEEP && cur != RT_REF_NONE) prefetchL1(sc.nodes + cur);
                 sm.cur[si] = cur;
                 modes = withSlot(modes, kI, mode, mode == MODE_SHADE ? 0u : sp);
                 if (COUNT) {
                     cnt[RT_CNT_INTERNAL] += wInternal; cnt[RT_CNT_POPS] += wPops;
                     ps[kI].work[0] += wInternal; ps[kI].work[3] += wPops;
+                }
+            }
+        } else if (stage == MODE_DEEP) {
+            // ------------------------------------------- DEEP stage: node records from global memory (L1/L2), loop pops
+            if (kD >= 0) {
+                const int si = kD * T + tid;
+                const float4 a = sm.A[si], b = sm.B[si];
+                const f3 o = mk3(a.x, a.y, a.z), inv = mk3(b.x, b.y, b.z);
+                const float bestT = a.w;
+                int32_t cur = sm.cur[si];
+                uint32_t sp = spOf(modes, kD);
+                int mode = MODE_DEEP;
+                uint2* const stack = sm.stack + si;
+                uint32_t wInternal = 0, wPops = 0;
+#pragma unroll 1
+                for (int s = 0; s < S; s++) {
+                    if (mode == MODE_DEEP) {
+                        bool goNear = false;
+                        if (cur != RT_REF_NONE) {
+                            const float4* np = reinterpret_cast<const float4*>(sc.nodes + cur);
+                            const float4 q0 = __ldg(np), q1 = __ldg(np + 1), q2 = __ldg(np + 2);
+                            const int2 refs = __ldg(reinterpret_cast<const int2*>(np + 3));
+                            const StepOut r = nodeMath(o, inv, bestT, q0, q1, q2, refs);
+                            if (COUNT) { wInternal++; wPops += r.hits; }
+                            if (r.pushFar) {
+                                stack[sp * STRIDE] = make_uint2(uint32_t(r.farRef), __float_as_uint(r.farT));
+                                sp++;
+                            }
+                            goNear = r.goNear;
+                            cur = r.nearRef;
+                        }
+                        if (goNear) mode = classify(cur, topCount);
+                        else popNext(stack, STRIDE, bestT, sp, cur, mode, topCount);
+                    }
+                }
+                if (mode == MODE_DEEP) prefetchL1(sc.nodes + cur);
+                sm.cur[si] = cur;
+                modes = withSlot(modes, kD, mode, mode == MODE_SHADE ? 0u : sp);
+                if (COUNT) {
+                    cnt[RT_CNT_INTERNAL] += wInternal; cnt[RT_CNT_POPS] += wPops;
+                    ps[kD].work[0] += wInternal; ps[kD].work[3] += wPops;
                 }
             }
         } else if (stage == MODE_LEAF) {
@@ -286,7 +336,8 @@ __global__ void __launch_bounds__(T, 1) rtPoolKernel(const __grid_constant__ Pas
                     sm.D[si] = make_float2(bestU, bestV);
                 }
                 int mode;
-                popNext(sm.stack + si, STRIDE, bestT, sp, cur, mode);
+                popNext(sm.stack + si, STRIDE, bestT, sp, cur, mode, topCount);
+                if (mode == MODE_DEEP) prefetchL1(sc.nodes + cur);
                 sm.cur[si] = cur;
                 modes = withSlot(modes, kL, mode, mode == MODE_SHADE ? 0u : sp);
             }
@@ -386,7 +437,7 @@ __global__ void __launch_bounds__(T, 1) rtPoolKernel(const __grid_constant__ Pas
                             s.rayColor = mul3(s.rayColor, hit.color);
                             s.bounce++;
                             pathEnds = hit.emission > 0.0f || s.bounce >= P.nBounces;
-                            if (!pathEnds) mode = beginRay<COUNT, T, K>(sc, sm, si, o, d, cnt, s);
+                            if (!pathEnds) mode = beginRay<COUNT, T, K>(sc, sm, si, o, d, cnt, s, topCount);
                         }
                     }
                     if (pixelEnds) {
@@ -426,7 +477,7 @@ __global__ void __launch_bounds__(T, 1) rtPoolKernel(const __grid_constant__ Pas
                                     s.primDir = primaryDirection(P, s.px, s.py, s.seed);
                                     s.fresh = 1;
                                     if (COUNT) cnt[RT_CNT_PATHS]++;
-                                    mode = beginRay<COUNT, T, K>(sc, sm, si, camPos, s.primDir, cnt, s);
+                                    mode = beginRay<COUNT, T, K>(sc, sm, si, camPos, s.primDir, cnt, s, topCount);
                                 }
                             }
                         }

@@ -80,5 +80,11 @@ struct PassParams {
     int32_t ownedW, ownedH;
     int32_t sumMode;                // 1: next = prev + curr (frame-sharded progressive mode), 0: running mean
     unsigned int* workCounter;      // persistent variant
+    // wavefront variant: queue of the pixels whose primary ray hit (stage 1 -> stage 2)
+    float4* queueA;                 // primary direction xyz, RNG state
+    float4* queueB;                 // primary hit t, u, v, slot
+    uint32_t* queuePix;             // px | py << 16
+    uint4* queueWork;               // counting passes only: work of the primary ray
+    unsigned int* queueCount;
     int32_t topCount;               // persistent variant: nodes [0, topCount) are staged in shared memory
 };

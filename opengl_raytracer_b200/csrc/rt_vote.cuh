@@ -21,7 +21,7 @@
 namespace vote {
 
 #ifndef RT_VOTE_THREADS
-#define RT_VOTE_THREADS 512
+#define RT_VOTE_THREADS 128
 #endif
 constexpr int kThreads = RT_VOTE_THREADS;
 constexpr int kScratchWords = 7;          // per lane: primary direction (3) + primary hit (slot, t, u, v)

@@ -9,7 +9,7 @@ from opengl_raytracer_b200 import rtlib
 
 pytestmark = pytest.mark.gpu
 
-VARIANTS = ["pixel", "persistent", "pool"]
+VARIANTS = ["pixel", "persistent", "pool", "wavefront"]
 EXACT_COUNTERS = ("rays", "internal", "leaves", "tri_tests", "hits", "pops", "paths")
 
 
