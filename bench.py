@@ -51,11 +51,10 @@ def load_peaks():
     return 6650.0, "fallback (B200_PROFILING.md)", 1965.0
 
 
-def algorithmic_bytes(cnt, traced_fraction=1.0):
+def algorithmic_bytes(cnt):
     """64 B per expanded internal node + 16 B per leaf entered + 40 B per triangle test + 68 B per
-    hit + 24 B (root bounds) per ray.  ``cnt`` are reference-equivalent counters; scaled to traced rays."""
-    b = 64 * cnt["internal"] + 16 * cnt["leaves"] + 40 * cnt["tri_tests"] + 68 * cnt["hits"] + 24 * cnt["rays"]
-    return b * traced_fraction
+    hit + 24 B (root bounds) per ray, over the work actually executed (``cnt``: counters of the traced rays)."""
+    return 64 * cnt["internal"] + 16 * cnt["leaves"] + 40 * cnt["tri_tests"] + 68 * cnt["hits"] + 24 * cnt["rays"]
 
 
 class ClockSampler:
@@ -104,40 +103,51 @@ def build_scene(name):
 
 
 # ------------------------------------------------------------------------------------ reference arm
-def run_reference(args):
-    """The reference's own shader math on the host cores: oracle/_ref (fragment.glsl compiled as C++) when it
-    was built, else the hand-written port.  A step is a bounded sample of the workload: one sample per pixel
-    of the same 4K frame on every `stride`-th 8-row band (frameNumber = step), all host threads."""
-    rank = int(os.environ.get("RANK", "0"))
-    if rank != 0:
-        return
+def cpu_sample_setup(stride):
+    """The bounded CPU sample both CPU legs time: the SAME frame as the GPU arm (frameNumber 0, 64 samples per
+    pixel, 4 bounces), restricted by the shader's own tile mask (fragment.glsl:382) to every `stride`-th
+    8-row band.  Returns (scene buffers, uniform block, distinct rays of the sample, description)."""
     sys.path.insert(0, os.path.join(ROOT, "oracle"))
     import oracle
-    kind = "reference" if oracle.have_ref() else "port"
-    impl = "ref" if kind == "reference" else "port"
     if not os.path.isfile(oracle.PORT_LIB):
         oracle.build_port()
     cfg, tris, boxes, indices = build_scene(WORKLOAD)
-    params = cfg.params(rays_per_pixel=1)
-    stride = args.cpu_band_stride
-    sample = params.replace(tileSizeX=cfg.width, numTilesX=1, tileSizeY=BAND_ROWS, numTilesY=stride, tileY=0)
-    rays, secs = [], []
+    params = cfg.params().replace(tileSizeX=cfg.width, numTilesX=1, tileSizeY=BAND_ROWS, numTilesY=stride, tileY=0,
+                                  frameNumber=0)
+    # untimed counting pass of the hand-written port: rays = raycast() calls the shader makes; the primary ray of a
+    # pixel-frame is the same ray for all its samples, so distinct rays = rays - (spp - 1) per pixel that casts
+    _, _, cnt = oracle.render_pass(tris, boxes, indices, params, impl="port", want_counters=True)
+    pixels = cnt["paths"] // max(cfg.rays_per_pixel, 1)
+    distinct = cnt["rays"] - (cfg.rays_per_pixel - 1) * pixels
+    desc = (f"{WORKLOAD}: frame 0 at {cfg.rays_per_pixel} spp on every {stride}th {BAND_ROWS}-row band of the "
+            f"{cfg.width}x{cfg.height} frame = {pixels} pixels, {cnt['rays']} raycast() calls, {distinct} distinct rays")
+    return oracle, (tris, boxes, indices), params, distinct, cnt["rays"], desc
+
+
+def run_reference(args):
+    """The reference's own shader math on the host cores: oracle/_ref (fragment.glsl compiled as C++) when it
+    was built, else the hand-written port; all host threads.  A step is one pass over the bounded sample above.
+    Rays are counted like the GPU arm counts them (distinct rays), so value ratios are frame-time ratios."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    oracle, scene, params, distinct, calls, desc = cpu_sample_setup(args.cpu_band_stride)
+    kind = "reference" if oracle.have_ref() else "port"
+    impl = "ref" if kind == "reference" else "port"
+    secs = []
     for step in range(args.warmup + args.steps):
-        p = sample.replace(frameNumber=step)
         t0 = time.perf_counter()
-        oracle.render_pass(tris, boxes, indices, p, impl=impl)
+        oracle.render_pass(*scene, params, impl=impl)
         dt = time.perf_counter() - t0
         if step >= args.warmup:
-            _, _, cnt = oracle.render_pass(tris, boxes, indices, p, impl="port", want_counters=True)   # untimed count
-            rays.append(cnt["rays"]); secs.append(dt)
-    value = sum(rays) / sum(secs) / 1e6
+            secs.append(dt)
+    value = distinct * len(secs) / sum(secs) / 1e6
     cores = oracle.num_threads(impl)
-    desc = (f"{WORKLOAD}: 1 sample/pixel on every {stride}th {BAND_ROWS}-row band of the 3840x2160 frame "
-            f"({sum(rays) // len(rays)} rays/step), frameNumber = step")
     line = {"impl": "reference", "metric": METRIC, "value": value, "unit": "Mrays/s", "n_gpus": args.gpus,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * sum(secs) / len(secs),
             "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "config": {"workload": f"{WORKLOAD}: models/dragon, 3840x2160, 64 spp, 4 bounces (bounded sample, see cpu_baseline.sample)"},
+            "raycast_calls_per_s_M": calls * len(secs) / sum(secs) / 1e6,
             "cpu_baseline": {"value": value, "unit": "Mrays/s", "cores": cores, "kind": kind, "sample": desc},
             "e2e": {"value": value, "unit": "Mrays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
@@ -219,7 +229,18 @@ def run_gpu(args):
         ctx.render_pass(0, 0, rank, flags=rtlib.PASS_COUNTERS | rtlib.PASS_SKIP_MASKED)
         mine = ctx.read_counters()
         total = dict(zip(rtlib.COUNTER_NAMES, sum_over_ranks([mine[k] for k in rtlib.COUNTER_NAMES])))
-        local_alg_bytes = algorithmic_bytes(mine, mine["rays_traced"] / max(mine["rays"], 1))
+        # work actually executed: the counters are reference-equivalent (the shader re-traces the primary ray for
+        # each of its spp samples); a primary-only counting pass gives that ray's work, traced exactly once
+        ctx.reset_counters()
+        ctx.set_params(distributed.band_params(params.replace(rays_per_pixel=1, nBounces=1), rank, world, BAND_ROWS))
+        ctx.target_clear()
+        ctx.render_pass(0, 0, rank, flags=rtlib.PASS_COUNTERS | rtlib.PASS_SKIP_MASKED)
+        prim = ctx.read_counters()
+        extra = max(cfg.rays_per_pixel - 1, 0)
+        traced = {k: mine[k] - extra * prim[k] for k in ("rays", "internal", "leaves", "tri_tests", "hits")}
+        assert traced["rays"] == mine["rays_traced"], (traced["rays"], mine["rays_traced"])
+        local_alg_bytes = algorithmic_bytes(traced)
+        ctx.set_params(params)
 
         for _ in range(warmup):
             step()
@@ -285,38 +306,63 @@ def run_gpu(args):
     main = measure(WORKLOAD, args.steps, args.warmup, True)
     cfg = main["cfg"]
     cnt = main["counters"]
-    achieved = main["local_alg_bytes"] / (main["kernel_ms"] * 1e-3) / 1e9
-    traffic = None
-    tpath = os.path.join(ROOT, "profiles", "traffic.json")
-    if os.path.isfile(tpath):
-        with open(tpath) as f:
-            traffic = json.load(f).get(WORKLOAD, {}).get("dram_bytes_per_launch")
+    # + 16 B written per pixel (RGBA32F target; frame 0 reads no previous texel)
+    fb_bytes = 16.0 * cfg.width * cfg.height / world
+    alg_bytes = main["local_alg_bytes"] + fb_bytes
+    achieved = alg_bytes / (main["kernel_ms"] * 1e-3) / 1e9
+    variant = args.variant
+    if variant == "auto":
+        variant = "persistent" if cfg.rays_per_pixel >= 16 else "pixel"          # rt_api.cu renderPass()
+    kernel = {"pixel": "rtPixelKernel", "persistent": "vote::rtVoteKernel", "pool": "pool::rtPoolKernel",
+              "wavefront": "wave::rtPrimaryKernel + wave::rtPathKernel"}[variant]
+    prof = {}
+    ppath = os.path.join(ROOT, "profiles", "bench_kernel_counters.json")
+    if os.path.isfile(ppath):
+        with open(ppath) as f:
+            prof = json.load(f).get(f"{WORKLOAD}/{variant}", {})
+    sm_count = torch.cuda.get_device_properties(dev).multi_processor_count
+    clock_mhz = (main["clocks"] or {}).get("sm_mhz") or sm_max
     roofline = {"bound": "hbm", "achieved": achieved, "peak": peak_gbs, "unit": "GB/s", "frac": achieved / peak_gbs,
-                "traffic": traffic, "peak_source": peak_src, "kernel": "rtPersistentKernel" if args.variant == "persistent" else "rtPixelKernel",
-                "kernel_ms": main["kernel_ms"],
-                "note": "algorithmic scene bytes (SURVEY §8d: 64 B/internal node, 16 B/leaf, 40 B/triangle test, 68 B/hit, "
-                        "24 B/ray) consumed per second by this rank's launch; the scene (8 MB) is L2/L1-resident so DRAM "
-                        "traffic is the framebuffer only and the binding limits are L1/L2 latency and warp issue"}
+                "traffic": prof.get("dram_bytes_per_launch"), "peak_source": peak_src, "kernel": kernel,
+                "kernel_ms": main["kernel_ms"], "algorithmic_bytes_per_launch": alg_bytes,
+                "note": "contract roofline: algorithmic bytes (SURVEY §8d: 64 B/internal node, 16 B/leaf, 40 B/triangle "
+                        "test, 68 B/hit, 24 B/ray of the rays actually traced, + 16 B/pixel of framebuffer) per second of "
+                        "this rank's launch, against the measured HBM copy peak.  The scene (8 MB) is L2/L1-resident by "
+                        "design, so DRAM traffic is the framebuffer only (see traffic) and the limits that bind are the "
+                        "L1 data pipe (one wavefront per divergent 16-byte node load) and warp issue: see l1_wavefronts / issue"}
+    if prof.get("inst_executed_per_launch"):
+        peak_issue = sm_count * 4 * clock_mhz * 1e6
+        ach = prof["inst_executed_per_launch"] / (main["kernel_ms"] * 1e-3)
+        roofline["issue"] = {"achieved": ach / 1e9, "peak": peak_issue / 1e9, "unit": "G warp-inst/s", "frac": ach / peak_issue,
+                             "lanes_per_inst": prof.get("lanes_per_inst"),
+                             "source": "inst per launch from the committed ncu capture of this workload, time live"}
+    if prof.get("l1_wavefronts_per_launch"):
+        peak_wf = sm_count * clock_mhz * 1e6
+        ach = prof["l1_wavefronts_per_launch"] / (main["kernel_ms"] * 1e-3)
+        roofline["l1_wavefronts"] = {"achieved": ach / 1e9, "peak": peak_wf / 1e9, "unit": "G wavefronts/s", "frac": ach / peak_wf,
+                                     "source": "l1tex data-pipe wavefronts per launch from the committed ncu capture, time live; "
+                                               "peak = 1 wavefront / cycle / SM"}
     line = {"metric": METRIC, "value": main["mrays_s"], "unit": "Mrays/s", "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": main["ms_per_step"], "higher_is_better": True, "scaling": "strong",
             "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "config": {"workload": f"{WORKLOAD}: models/dragon (37,986 triangles) under open sky, {cfg.width}x{cfg.height}, "
                                    f"{cfg.rays_per_pixel} spp, {cfg.bounces} bounces, 1 frame",
                        "parallelism": f"tile mode: {world} x interleaved {BAND_ROWS}-row bands, NCCL gather to rank 0",
-                       "l2": "256 MiB memset between steps, inside the timed region", "variant": args.variant},
+                       "l2": "256 MiB memset between steps, inside the timed region", "variant": variant,
+                       "ray_unit": "distinct rays traced: raycast() calls with the primary ray of a pixel-frame counted once, not once per sample"},
             "ms_per_frame": main["ms_per_step"], "rays_per_step": cnt["rays_traced"],
             "reference_equivalent": {"rays_per_step": cnt["rays"], "mrays_s": main["ref_equiv_mrays_s"]},
             "e2e": main["e2e"], "gpu_launches": main["launches"], "roofline": roofline, "clocks": main["clocks"]}
 
     if world == 1 and not args.no_cpu:
-        line["cpu_baseline"] = cpu_baseline(ctx, rtlib, main, args)
+        line["cpu_baseline"] = cpu_baseline(args)
     if not args.no_box:
-        box = measure(BOX_WORKLOAD, max(1, args.steps // 2), 1, False)
+        box = measure(BOX_WORKLOAD, max(1, args.steps // 2), 3, False)
         bc = box["counters"]
         line["box_variant"] = {"workload": f"{BOX_WORKLOAD}: dragon inside the main.py room, same size/spp/bounces",
                                "value": box["mrays_s"], "unit": "Mrays/s", "ms_per_frame": box["ms_per_step"],
                                "rays_per_step": bc["rays_traced"], "kernel_ms": box["kernel_ms"],
-                               "roofline_achieved_gbs": box["local_alg_bytes"] / (box["kernel_ms"] * 1e-3) / 1e9,
+                               "roofline_achieved_gbs": (box["local_alg_bytes"] + fb_bytes) / (box["kernel_ms"] * 1e-3) / 1e9,
                                "per_ray": {"internal": bc["internal"] / bc["rays"], "tri_tests": bc["tri_tests"] / bc["rays"]}}
     if rank == 0:
         print(json.dumps(line), flush=True)
@@ -325,33 +371,21 @@ def run_gpu(args):
         dist.destroy_process_group()
 
 
-def cpu_baseline(ctx, rtlib, main, args):
-    """The reference shader (oracle/_ref, else the port) on the host cores: whole 4K frames of the workload at
-    one sample per pixel (frameNumber 0, 1, ...) until about `cpu_seconds` of CPU work; rays counted by a GPU
-    counting pass of the same frames (same rays: the parity tests pin the counters to the oracle's)."""
-    sys.path.insert(0, os.path.join(ROOT, "oracle"))
-    import oracle
+def cpu_baseline(args):
+    """The reference shader (oracle/_ref, else the port) on the host cores, on the same bounded sample the
+    --impl reference arm times, repeated until about `cpu_seconds` of CPU work."""
+    oracle, scene, params, distinct, calls, desc = cpu_sample_setup(args.cpu_band_stride)
     kind = "reference" if oracle.have_ref() else "port"
     impl = "ref" if kind == "reference" else "port"
-    if not os.path.isfile(oracle.PORT_LIB):
-        oracle.build_port()
-    cfg = main["cfg"]
-    tris, boxes, indices = main["scene"]
-    params = cfg.params(rays_per_pixel=1)
-    ctx.set_params(params)
-    secs, rays, frames = 0.0, 0, 0
-    while secs < args.cpu_seconds and frames < 64:
-        p = params.replace(frameNumber=frames)
+    secs, reps = 0.0, 0
+    while secs < args.cpu_seconds and reps < 16:
         t0 = time.perf_counter()
-        oracle.render_pass(tris, boxes, indices, p, impl=impl)
+        oracle.render_pass(*scene, params, impl=impl)
         secs += time.perf_counter() - t0
-        ctx.reset_counters(); ctx.target_clear()
-        ctx.render_pass(frames, 0, 0, flags=rtlib.PASS_COUNTERS)
-        rays += ctx.read_counters()["rays"]
-        frames += 1
-    return {"value": rays / secs / 1e6, "unit": "Mrays/s", "cores": oracle.num_threads(impl), "kind": kind,
-            "sample": f"{frames} full {cfg.width}x{cfg.height} frame(s) of {WORKLOAD} at 1 sample/pixel "
-                      f"({rays} rays, {secs:.1f} s)"}
+        reps += 1
+    return {"value": distinct * reps / secs / 1e6, "unit": "Mrays/s", "cores": oracle.num_threads(impl), "kind": kind,
+            "raycast_calls_per_s_M": calls * reps / secs / 1e6,
+            "sample": f"{reps} x [{desc}], {secs:.1f} s"}
 
 
 def main():
@@ -365,7 +399,7 @@ def main():
     ap.add_argument("--no-box", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--cpu-seconds", type=float, default=12.0)
-    ap.add_argument("--cpu-band-stride", type=int, default=1)
+    ap.add_argument("--cpu-band-stride", type=int, default=8)
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)
