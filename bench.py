@@ -151,7 +151,7 @@ def run_reference(args):
             "cpu_baseline": {"value": value, "unit": "Mrays/s", "cores": cores, "kind": kind, "sample": desc},
             "e2e": {"value": value, "unit": "Mrays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
-    print(json.dumps(line), flush=True)
+    print_line(line)
 
 
 # ------------------------------------------------------------------------------------------ GPU arm
@@ -323,7 +323,7 @@ def run_gpu(args):
     sm_count = torch.cuda.get_device_properties(dev).multi_processor_count
     clock_mhz = (main["clocks"] or {}).get("sm_mhz") or sm_max
     roofline = {"bound": "hbm", "achieved": achieved, "peak": peak_gbs, "unit": "GB/s", "frac": achieved / peak_gbs,
-                "traffic": prof.get("dram_bytes_per_launch"), "peak_source": peak_src, "kernel": kernel,
+                "traffic": (prof["dram_bytes_per_launch"] / world) if prof.get("dram_bytes_per_launch") else None, "peak_source": peak_src, "kernel": kernel,
                 "kernel_ms": main["kernel_ms"], "algorithmic_bytes_per_launch": alg_bytes,
                 "note": "contract roofline: algorithmic bytes (SURVEY §8d: 64 B/internal node, 16 B/leaf, 40 B/triangle "
                         "test, 68 B/hit, 24 B/ray of the rays actually traced, + 16 B/pixel of framebuffer) per second of "
@@ -332,13 +332,13 @@ def run_gpu(args):
                         "L1 data pipe (one wavefront per divergent 16-byte node load) and warp issue: see l1_wavefronts / issue"}
     if prof.get("inst_executed_per_launch"):
         peak_issue = sm_count * 4 * clock_mhz * 1e6
-        ach = prof["inst_executed_per_launch"] / (main["kernel_ms"] * 1e-3)
+        ach = prof["inst_executed_per_launch"] / world / (main["kernel_ms"] * 1e-3)     # N > 1: this rank's 1/N share (approx.)
         roofline["issue"] = {"achieved": ach / 1e9, "peak": peak_issue / 1e9, "unit": "G warp-inst/s", "frac": ach / peak_issue,
                              "lanes_per_inst": prof.get("lanes_per_inst"),
                              "source": "inst per launch from the committed ncu capture of this workload, time live"}
     if prof.get("l1_wavefronts_per_launch"):
         peak_wf = sm_count * clock_mhz * 1e6
-        ach = prof["l1_wavefronts_per_launch"] / (main["kernel_ms"] * 1e-3)
+        ach = prof["l1_wavefronts_per_launch"] / world / (main["kernel_ms"] * 1e-3)
         roofline["l1_wavefronts"] = {"achieved": ach / 1e9, "peak": peak_wf / 1e9, "unit": "G wavefronts/s", "frac": ach / peak_wf,
                                      "source": "l1tex data-pipe wavefronts per launch from the committed ncu capture, time live; "
                                                "peak = 1 wavefront / cycle / SM"}
@@ -365,7 +365,7 @@ def run_gpu(args):
                                "roofline_achieved_gbs": (box["local_alg_bytes"] + fb_bytes) / (box["kernel_ms"] * 1e-3) / 1e9,
                                "per_ray": {"internal": bc["internal"] / bc["rays"], "tri_tests": bc["tri_tests"] / bc["rays"]}}
     if rank == 0:
-        print(json.dumps(line), flush=True)
+        print_line(line)
     ctx.close()
     if world > 1:
         dist.destroy_process_group()
@@ -389,6 +389,13 @@ def cpu_baseline(args):
 
 
 def main():
+    # stdout carries exactly one JSON line: libraries that print there (NCCL's version banner) go to stderr
+    real_stdout = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
+    global print_line
+    def print_line(obj):
+        real_stdout.write(json.dumps(obj) + "\n")
+        real_stdout.flush()
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=5)

@@ -8,6 +8,7 @@
 #include <cuda_runtime.h>
 
 #include <algorithm>
+#include <cstdio>
 #include <cstdlib>
 
 #include "../../include/rt_b200.h"
@@ -197,11 +198,8 @@ cudaError_t rtLaunchPersistent(const PassParams& Pin, bool count, bool ids, int 
     PassParams P = Pin;
     if (P.ownedW <= 0 || P.ownedH <= 0) return cudaSuccess;
     const size_t base = vote::smemBytes(P.scene.stackDepth);
-    // optional staging of the tree top in shared memory (measured: no gain at this CTA size; off by default)
-    long long top = 0;
-    if (const char* e = getenv("RT_VOTE_TOP_NODES")) top = std::min<long long>(atoll(e), (long long)((96 * 1024 - base) / 64));
-    P.topCount = int(std::min<long long>(top, P.scene.nNodes));
-    const size_t smem = base + vote::topBytes(P.topCount);
+    if (const char* e = getenv("RT_VOTE_TUNE")) sscanf(e, "%d,%d", &P.tune[0], &P.tune[1]);
+    const size_t smem = base;
     cudaError_t e = cudaMemsetAsync(P.workCounter, 0, sizeof(unsigned int), stream);
     if (e != cudaSuccess) return e;
     // no more CTAs than there is work for: one warp per 32 pixel indices
@@ -215,6 +213,7 @@ cudaError_t rtLaunchPersistent(const PassParams& Pin, bool count, bool ids, int 
         e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSm, vote::rtVoteKernel<C, I>, vote::kThreads, smem); \
         if (e != cudaSuccess) return e;                                                                          \
         if (perSm < 1) perSm = 1;                                                                                \
+        if (const char* v = getenv("RT_VOTE_CTAS")) perSm = std::max(1, std::min(perSm, atoi(v)));                \
         vote::rtVoteKernel<C, I><<<std::min(sms * perSm, std::max(needed, 1)), vote::kThreads, smem, stream>>>(P); \
     } while (0)
     if (count && ids) RT_LAUNCH(true, true);

@@ -86,5 +86,6 @@ struct PassParams {
     uint32_t* queuePix;             // px | py << 16
     uint4* queueWork;               // counting passes only: work of the primary ray
     unsigned int* queueCount;
+    int32_t tune[4];                // scheduling thresholds (0 = built-in default); bench tooling only
     int32_t topCount;               // persistent variant: nodes [0, topCount) are staged in shared memory
 };

@@ -1,20 +1,26 @@
 // rt_vote.cuh — variant PERSISTENT: persistent warps, warp-vote scheduled state machine.
 //
 // Why: in the one-thread-per-pixel kernel every lane walks its own sample/bounce/traversal loops, so a warp
-// pays max-over-lanes at every level, and — worse — the rare, expensive blocks (leaf triangle tests: 3 % of the
-// node steps; shading) are executed for one or two lanes at a time (ncu capture B: 11.3 of 32 lanes active,
-// leaf/pop code with 4-7 lanes).  Here each lane is a small state machine
+// pays max-over-lanes at every level, and the rare, expensive blocks (leaf triangle tests, shading) are executed
+// for two to five lanes at a time (profiles/r01_ncu_notes.md).  Here each lane is a small state machine
 //
 //     INTERNAL (at an internal node)   LEAF (at a leaf)   SHADE (traversal finished / needs a pixel)   DONE
 //
 // and every iteration of the warp's loop executes exactly ONE section, chosen by ballot: lanes that reach a
-// leaf or finish a ray wait until enough lanes are in the same state (or nobody else can make progress), so
-// the expensive sections run densely populated and the hot internal-node section is never interleaved with
-// them.  All branches that select code are warp-uniform, so lanes stay converged.  Lanes fetch their next
-// pixel from a global counter (warp-aggregated atomic), which also removes the sky-versus-mesh imbalance.
+// leaf or finish a ray wait until enough lanes are in the same state (or nobody else can make progress), so the
+// expensive sections run densely populated and the hot internal-node section is never interleaved with them.
+// All branches that select code are warp-uniform, so lanes stay converged.  Lanes fetch their next pixel from a
+// global counter (warp-aggregated atomic), which also removes the sky-versus-mesh imbalance.
+//
+// Second version (ncu capture G): the INTERNAL section runs a burst of kBurst node steps per vote (the ballots
+// were 10 % of the instructions); a step pops at most once, branch-free (the pop loop ran at 4 of 32 lanes);
+// everything about a pixel-frame's first bounce that does not depend on the sample — surface point, normal,
+// material, normalised mirror direction, next origin, emitted light, throughput — is computed once when the
+// primary ray lands and parked in shared memory (shading was 25 % of the instructions at 4-5 lanes).
 //
 // Per-ray semantics are exactly those of traverse()/pixelFrame() in rt_device.cuh / rt_kernels.cu — the
-// visiting order inside a ray never changes, only which lanes run when.
+// visiting order inside a ray never changes, only which lanes run when; hoisting a computation out of the
+// sample loop does not change its result.
 #pragma once
 #include "rt_shade.cuh"
 
@@ -24,21 +30,20 @@ namespace vote {
 #define RT_VOTE_THREADS 128
 #endif
 constexpr int kThreads = RT_VOTE_THREADS;
-constexpr int kScratchWords = 7;          // per lane: primary direction (3) + primary hit (slot, t, u, v)
+constexpr int kBurst = 4;
+// per lane: normal0 (3), k0, s1 (3), origin0 (3), incoming0 (3), rayColor0 (3), stop0
+constexpr int kScratchWords = 17;
 constexpr int MODE_INTERNAL = 0, MODE_LEAF = 1, MODE_SHADE = 2, MODE_DONE = 3;
 
 inline size_t smemBytes(int stackDepth) {
     return size_t(stackDepth) * kThreads * sizeof(uint2) + size_t(kScratchWords) * kThreads * sizeof(uint32_t);
 }
-// Top of the tree in shared memory (nodes are numbered breadth-first, so "the first topCount nodes" are the top
-// levels): four float4 arrays (q0 | q1 | q2 | refs) so that lanes reading record `cur` spread over all bank groups.
-inline size_t topBytes(int topCount) { return size_t(topCount) * 64; }
 
 struct Lane {
     // traversal
     f3 o, d, inv;
     RayHit best;
-    int32_t cur;
+    int32_t cur;      // RT_REF_NONE while INTERNAL: "the last pop was culled, pop again"
     uint32_t sp;
     int32_t mode;
     // path
@@ -79,40 +84,36 @@ RT_DEV void popNext(Lane& L, const uint2* stack, uint32_t stride) {
     L.mode = found ? (L.cur >= 0 ? MODE_INTERNAL : MODE_LEAF) : MODE_SHADE;
 }
 
-// One internal-node step (fragment.glsl:281-304), see traverse() for the order-preserving details.
+// One internal-node step (fragment.glsl:281-304), see traverse() for the order-preserving details.  The step
+// pops at most ONE entry: closestT only changes in the LEAF section, so a popped entry fails the cull only if a
+// leaf improved closestT after it was pushed; then cur = RT_REF_NONE and the lane pops again on its next step.
 template <bool COUNT>
-RT_DEV void stepInternal(const DeviceScene& sc, Lane& L, uint2* stack, uint32_t stride, uint32_t* cnt,
-                         const float4* top, int topCount) {
-    float4 q0, q1, q2;
-    int2 refs;
-    if (L.cur < topCount) {
-        q0 = top[L.cur]; q1 = top[topCount + L.cur]; q2 = top[2 * topCount + L.cur];
-        const float4 r = top[3 * topCount + L.cur];
-        refs = make_int2(__float_as_int(r.x), __float_as_int(r.y));
-    } else {
+RT_DEV void stepInternal(const DeviceScene& sc, Lane& L, uint2* stack, uint32_t stride, uint32_t* cnt) {
+    bool goNear = false;
+    if (L.cur != RT_REF_NONE) {
         const float4* np = reinterpret_cast<const float4*>(sc.nodes + L.cur);
-        q0 = __ldg(np); q1 = __ldg(np + 1); q2 = __ldg(np + 2);
-        refs = __ldg(reinterpret_cast<const int2*>(np + 3));
-    }
-    bool hitA, hitB;
-    const float tA = slabTest(L.o, L.inv, q0.x, q0.y, q0.z, q0.w, q1.x, q1.y, hitA);
-    const float tB = slabTest(L.o, L.inv, q1.z, q1.w, q2.x, q2.y, q2.z, q2.w, hitB);
-    if (COUNT) { cnt[RT_CNT_INTERNAL]++; cnt[RT_CNT_POPS] += (hitA ? 1u : 0u) + (hitB ? 1u : 0u); }
-    const bool aFirst = hitA && (!hitB || tA < tB);
-    const int32_t nearRef = aFirst ? refs.x : refs.y, farRef = aFirst ? refs.y : refs.x;
-    const float nearT = aFirst ? tA : tB, farT = aFirst ? tB : tA;
-    const bool goNear = (hitA || hitB) && !(nearT > L.best.t);
-    const bool pushFar = hitA && hitB && !(farT > L.best.t);
-    if (pushFar) {
-        stack[L.sp * stride] = make_uint2(uint32_t(farRef), __float_as_uint(farT));
-        L.sp++;
-    }
-    if (goNear) {
+        const float4 q0 = __ldg(np), q1 = __ldg(np + 1), q2 = __ldg(np + 2);
+        const int2 refs = __ldg(reinterpret_cast<const int2*>(np + 3));
+        bool hitA, hitB;
+        const float tA = slabTest(L.o, L.inv, q0.x, q0.y, q0.z, q0.w, q1.x, q1.y, hitA);
+        const float tB = slabTest(L.o, L.inv, q1.z, q1.w, q2.x, q2.y, q2.z, q2.w, hitB);
+        if (COUNT) { cnt[RT_CNT_INTERNAL]++; cnt[RT_CNT_POPS] += (hitA ? 1u : 0u) + (hitB ? 1u : 0u); }
+        const bool aFirst = hitA && (!hitB || tA < tB);
+        const int32_t nearRef = aFirst ? refs.x : refs.y, farRef = aFirst ? refs.y : refs.x;
+        const float nearT = aFirst ? tA : tB, farT = aFirst ? tB : tA;
+        goNear = (hitA || hitB) && !(nearT > L.best.t);
+        const bool pushFar = hitA && hitB && !(farT > L.best.t);
+        if (pushFar) {
+            stack[L.sp * stride] = make_uint2(uint32_t(farRef), __float_as_uint(farT));
+            L.sp++;
+        }
         L.cur = nearRef;
-        L.mode = nearRef >= 0 ? MODE_INTERNAL : MODE_LEAF;
-    } else {
-        popNext(L, stack, stride);
     }
+    const bool havePop = !goNear && L.sp > 0;
+    uint2 e = make_uint2(uint32_t(RT_REF_NONE), 0u);
+    if (havePop) { L.sp--; e = stack[L.sp * stride]; }
+    if (!goNear) L.cur = (__uint_as_float(e.y) > L.best.t) ? RT_REF_NONE : int32_t(e.x);
+    L.mode = (goNear || havePop) ? (L.cur >= 0 ? MODE_INTERNAL : MODE_LEAF) : MODE_SHADE;
 }
 
 // One leaf (fragment.glsl:266-279): every triangle in slot order, first found wins ties; then pop.
@@ -135,14 +136,20 @@ RT_DEV void stepLeaf(const DeviceScene& sc, Lane& L, const uint2* stack, uint32_
     popNext(L, stack, stride);
 }
 
+// fragment.glsl:234-240 with the specular half precomputed: s1 = normalize(specular) * t, k0 = 1 - t, t = 1 - roughness.
+RT_DEV f3 lerpDirPre(f3 diffuse, float k0, f3 s1) {
+    const f3 zero = mk3(0.f, 0.f, 0.f);
+    const f3 d0 = length3(diffuse) > 0.0f ? normalize3(diffuse) : zero;
+    return normalize3(add3(scale3(d0, k0), s1));
+}
 
 // Scheduling thresholds: a section runs when at least this many lanes wait for it, or when no lane can do
-// anything cheaper.  Tuned on B200 (profiles/r01_ncu_notes.md).
+// anything cheaper.  Defaults tuned on B200 (profiles/r01_variants.md); PassParams.tune overrides (bench tooling).
 #ifndef RT_VOTE_LEAF_LANES
 #define RT_VOTE_LEAF_LANES 8
 #endif
 #ifndef RT_VOTE_SHADE_LANES
-#define RT_VOTE_SHADE_LANES 8
+#define RT_VOTE_SHADE_LANES 12
 #endif
 
 template <bool COUNT, bool IDS>
@@ -152,20 +159,14 @@ __global__ void __launch_bounds__(kThreads) rtVoteKernel(const __grid_constant__
     const uint32_t lane = threadIdx.x & 31u;
     uint2* const stack = smem + threadIdx.x;
     const uint32_t stride = kThreads;
-    uint32_t* const scratch = reinterpret_cast<uint32_t*>(smem + size_t(sc.stackDepth) * kThreads) + threadIdx.x;
-    float4* const top = reinterpret_cast<float4*>(reinterpret_cast<uint32_t*>(smem + size_t(sc.stackDepth) * kThreads) +
-                                                  size_t(kScratchWords) * kThreads);
-    const int topCount = P.topCount;
-    for (int i = threadIdx.x; i < topCount * 4; i += kThreads) {
-        const int node = i >> 2, part = i & 3;
-        top[part * topCount + node] = __ldg(reinterpret_cast<const float4*>(sc.nodes + node) + part);
-    }
-    __syncthreads();
+    float* const scratch = reinterpret_cast<float*>(smem + size_t(sc.stackDepth) * kThreads) + threadIdx.x;
+    const int leafLanes = P.tune[0] > 0 ? P.tune[0] : RT_VOTE_LEAF_LANES;
+    const int shadeLanes = P.tune[1] > 0 ? P.tune[1] : RT_VOTE_SHADE_LANES;
 
     const int tilesX = (P.ownedW + 7) >> 3, tilesY = (P.ownedH + 3) >> 2;
     const unsigned int totalIdx = (unsigned int)tilesX * (unsigned int)tilesY * 32u;
     const f3 camPos = ld3(P.camPos);
-    const f3 zero = mk3(0.f, 0.f, 0.f);
+    const f3 zero = mk3(0.f, 0.f, 0.f), one = mk3(1.f, 1.f, 1.f);
     const f3 sky = scale3(mk3(0.1f, 0.6f, 0.92f), P.skyBrightness);   // fragment.glsl:242-244, :388
     const bool lambertian = P.lambertian != 0;
     const bool degenerate = P.nBounces <= 0 || P.raysPerPixel <= 0;   // no ray is ever cast
@@ -189,17 +190,19 @@ __global__ void __launch_bounds__(kThreads) rtVoteKernel(const __grid_constant__
         const uint32_t mS = __ballot_sync(0xffffffffu, L.mode == MODE_SHADE);
         if ((mI | mL | mS) == 0u) break;
 
-        if (__popc(mS) >= RT_VOTE_SHADE_LANES || (mI | mL) == 0u) {
+        // thresholds shrink with the number of lanes that still have work: a sparsely populated warp (the tail of a
+        // frame, or a rank's thin share of a tile-sharded frame) must not make its few rays wait for each other —
+        // that wait is pure latency on the serial sample chain of a pixel (measured: 12 ms floor at 1/8 frame)
+        const int active = __popc(mI | mL | mS);
+        const int shadeT = min(shadeLanes, max(1, (active * 3) >> 3));
+        const int leafT = min(leafLanes, max(1, active >> 2));
+        if (__popc(mS) >= shadeT || (mI | mL) == 0u) {
             // ------------------------------------------------------------------ SHADE section
             if (L.mode == MODE_SHADE && !L.needPixel) {
-                bool pathEnds = false, pixelEnds = false;
+                bool pathEnds = false, pixelEnds = false, startSample = false;
                 if (L.fresh) {
-                    // the pixel's primary ray just finished: keep its hit for the other samples (:361-362)
+                    // the pixel's primary ray just landed (every sample of the pixel-frame shares it, :361-362)
                     L.fresh = false;
-                    scratch[3 * kThreads] = uint32_t(L.best.slot);
-                    scratch[4 * kThreads] = __float_as_uint(L.best.t);
-                    scratch[5 * kThreads] = __float_as_uint(L.best.u);
-                    scratch[6 * kThreads] = __float_as_uint(L.best.v);
                     if (COUNT) {
                         primWork[0] = cnt[RT_CNT_INTERNAL] - primBase[0]; primWork[1] = cnt[RT_CNT_LEAVES] - primBase[1];
                         primWork[2] = cnt[RT_CNT_TRI_TESTS] - primBase[2]; primWork[3] = cnt[RT_CNT_POPS] - primBase[3];
@@ -220,10 +223,28 @@ __global__ void __launch_bounds__(kThreads) rtVoteKernel(const __grid_constant__
                             cnt[RT_CNT_POPS] += primWork[3] * (P.raysPerPixel - 1);
                         }
                         pixelEnds = true;
+                    } else {
+                        // once per pixel-frame: the part of bounce 0 that does not depend on the sample (:319-334)
+                        const SurfaceHit hit0 = resolveHit(sc, L.best, camPos, L.d);
+                        const f3 spec0 = reflect3(L.d, hit0.normal);
+                        const float t0 = sub(1.0f, hit0.roughness);
+                        const f3 s1 = scale3(length3(spec0) > 0.0f ? normalize3(spec0) : zero, t0);
+                        const f3 origin0 = add3(hit0.point, scale3(hit0.normal, 1e-4f));
+                        f3 emitted0 = scale3(hit0.emissionColor, hit0.emission);
+                        if (lambertian) emitted0 = scale3(emitted0, 2.0f);
+                        const f3 incoming0 = add3(zero, mul3(emitted0, one));
+                        const f3 rayColor0 = mul3(one, hit0.color);
+                        scratch[0 * kThreads] = hit0.normal.x; scratch[1 * kThreads] = hit0.normal.y; scratch[2 * kThreads] = hit0.normal.z;
+                        scratch[3 * kThreads] = sub(1.0f, t0);
+                        scratch[4 * kThreads] = s1.x; scratch[5 * kThreads] = s1.y; scratch[6 * kThreads] = s1.z;
+                        scratch[7 * kThreads] = origin0.x; scratch[8 * kThreads] = origin0.y; scratch[9 * kThreads] = origin0.z;
+                        scratch[10 * kThreads] = incoming0.x; scratch[11 * kThreads] = incoming0.y; scratch[12 * kThreads] = incoming0.z;
+                        scratch[13 * kThreads] = rayColor0.x; scratch[14 * kThreads] = rayColor0.y; scratch[15 * kThreads] = rayColor0.z;
+                        scratch[16 * kThreads] = hit0.emission > 0.0f ? 1.0f : 0.0f;
+                        startSample = true;
                     }
-                }
-                if (!pixelEnds) {
-                    // one iteration of raytrace()'s loop body (fragment.glsl:313-347) for the ray just traced
+                } else {
+                    // one iteration of raytrace()'s loop body (fragment.glsl:313-347) for the (non-primary) ray just traced
                     if (COUNT) cnt[RT_CNT_RAYS]++;
                     if (L.best.slot >= 0) {
                         if (COUNT) cnt[RT_CNT_HITS]++;
@@ -243,28 +264,45 @@ __global__ void __launch_bounds__(kThreads) rtVoteKernel(const __grid_constant__
                         L.incoming = add3(L.incoming, sky);   // un-attenuated, as the shader does (:343)
                         pathEnds = true;
                     }
-                    if (pathEnds) {
-                        L.color = add3(L.color, L.incoming);   // trace(), :359
-                        L.sample++;
-                        if (L.sample >= P.raysPerPixel) {
-                            pixelEnds = true;
-                        } else {
-                            // next sample: same primary ray, RNG state carried over (:358-363)
-                            L.incoming = zero; L.rayColor = mk3(1.f, 1.f, 1.f); L.bounce = 0;
-                            L.o = camPos;
-                            L.d = mk3(__uint_as_float(scratch[0]), __uint_as_float(scratch[kThreads]),
-                                      __uint_as_float(scratch[2 * kThreads]));
-                            L.best.slot = int32_t(scratch[3 * kThreads]);
-                            L.best.t = __uint_as_float(scratch[4 * kThreads]);
-                            L.best.u = __uint_as_float(scratch[5 * kThreads]);
-                            L.best.v = __uint_as_float(scratch[6 * kThreads]);
-                            L.mode = MODE_SHADE;
-                            if (COUNT) {
-                                cnt[RT_CNT_PATHS]++;
-                                cnt[RT_CNT_INTERNAL] += primWork[0]; cnt[RT_CNT_LEAVES] += primWork[1];
-                                cnt[RT_CNT_TRI_TESTS] += primWork[2]; cnt[RT_CNT_POPS] += primWork[3];
-                            }
+                }
+                if (pathEnds) {
+                    L.color = add3(L.color, L.incoming);   // trace(), :359
+                    L.sample++;
+                    if (L.sample >= P.raysPerPixel) pixelEnds = true;
+                    else startSample = true;   // next sample: same primary ray, RNG state carried over (:358-363)
+                }
+                if (startSample) {
+                    // bounce 0 of a sample: the cached primary hit
+                    if (COUNT) {
+                        cnt[RT_CNT_RAYS]++; cnt[RT_CNT_HITS]++;
+                        if (L.sample > 0) {
+                            cnt[RT_CNT_PATHS]++;
+                            cnt[RT_CNT_INTERNAL] += primWork[0]; cnt[RT_CNT_LEAVES] += primWork[1];
+                            cnt[RT_CNT_TRI_TESTS] += primWork[2]; cnt[RT_CNT_POPS] += primWork[3];
                         }
+                    }
+                    const f3 incoming0 = mk3(scratch[10 * kThreads], scratch[11 * kThreads], scratch[12 * kThreads]);
+                    if (scratch[16 * kThreads] != 0.0f || P.nBounces <= 1) {
+                        // the path ends at bounce 0 (emissive surface or no further bounce) for every remaining sample:
+                        // each adds 0 + incoming0; the RNG draws of diffuse() never reach the output
+                        const int remaining = P.raysPerPixel - L.sample;
+                        for (int s = 0; s < remaining; s++) L.color = add3(L.color, incoming0);
+                        if (COUNT) {
+                            cnt[RT_CNT_RAYS] += remaining - 1; cnt[RT_CNT_HITS] += remaining - 1; cnt[RT_CNT_PATHS] += remaining - 1;
+                            cnt[RT_CNT_INTERNAL] += primWork[0] * (remaining - 1); cnt[RT_CNT_LEAVES] += primWork[1] * (remaining - 1);
+                            cnt[RT_CNT_TRI_TESTS] += primWork[2] * (remaining - 1); cnt[RT_CNT_POPS] += primWork[3] * (remaining - 1);
+                        }
+                        pixelEnds = true;
+                    } else {
+                        const f3 normal0 = mk3(scratch[0 * kThreads], scratch[1 * kThreads], scratch[2 * kThreads]);
+                        const f3 s1 = mk3(scratch[4 * kThreads], scratch[5 * kThreads], scratch[6 * kThreads]);
+                        const f3 dDiff0 = diffuseDir(normal0, L.seed, lambertian);
+                        L.d = lerpDirPre(dDiff0, scratch[3 * kThreads], s1);
+                        L.o = mk3(scratch[7 * kThreads], scratch[8 * kThreads], scratch[9 * kThreads]);
+                        L.incoming = incoming0;
+                        L.rayColor = mk3(scratch[13 * kThreads], scratch[14 * kThreads], scratch[15 * kThreads]);
+                        L.bounce = 1;
+                        beginRay<COUNT>(sc, L, cnt);
                     }
                 }
                 if (pixelEnds) {
@@ -293,7 +331,7 @@ __global__ void __launch_bounds__(kThreads) rtVoteKernel(const __grid_constant__
                             L.needPixel = false;
                             L.px = ownedToPixel(ox, P.tileSizeX, P.numTilesX, P.tileX);
                             L.py = ownedToPixel(oy, P.tileSizeY, P.numTilesY, P.tileY);
-                            L.color = zero; L.incoming = zero; L.rayColor = mk3(1.f, 1.f, 1.f);
+                            L.color = zero; L.incoming = zero; L.rayColor = one;
                             L.sample = 0; L.bounce = 0;
                             if (degenerate) {
                                 const size_t at = size_t(L.py) * size_t(P.width) + size_t(L.px);
@@ -304,9 +342,6 @@ __global__ void __launch_bounds__(kThreads) rtVoteKernel(const __grid_constant__
                             } else {
                                 L.o = camPos;
                                 L.d = primaryDirection(P, L.px, L.py, L.seed);
-                                scratch[0] = __float_as_uint(L.d.x);
-                                scratch[kThreads] = __float_as_uint(L.d.y);
-                                scratch[2 * kThreads] = __float_as_uint(L.d.z);
                                 L.fresh = true;
                                 if (COUNT) {
                                     cnt[RT_CNT_PATHS]++;
@@ -319,12 +354,14 @@ __global__ void __launch_bounds__(kThreads) rtVoteKernel(const __grid_constant__
                     }
                 }
             }
-        } else if (__popc(mL) >= RT_VOTE_LEAF_LANES || mI == 0u) {
+        } else if (__popc(mL) >= leafT || mI == 0u) {
             // ------------------------------------------------------------------- LEAF section
             if (L.mode == MODE_LEAF) stepLeaf<COUNT>(sc, L, stack, stride, cnt);
         } else {
-            // --------------------------------------------------------------- INTERNAL section
-            if (L.mode == MODE_INTERNAL) stepInternal<COUNT>(sc, L, stack, stride, cnt, top, topCount);
+            // ------------------------------------------- INTERNAL section: a burst of node steps per vote
+#pragma unroll 1
+            for (int s = 0; s < kBurst; s++)
+                if (L.mode == MODE_INTERNAL) stepInternal<COUNT>(sc, L, stack, stride, cnt);
         }
     }
 
