@@ -401,7 +401,7 @@ def main():
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--variant", default="auto", choices=["auto", "pixel", "persistent", "wavefront", "pool"])
+    ap.add_argument("--variant", default="auto", choices=["auto", "pixel", "persistent", "wavefront", "pool", "samples"])
     ap.add_argument("--spp", type=int, default=0, help="override samples per pixel (not a valid bench number)")
     ap.add_argument("--no-box", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")

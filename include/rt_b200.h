@@ -76,6 +76,9 @@ enum {
     RT_VARIANT_PIXEL = 1,       /* one thread per pixel, whole pixel-frame in one kernel */
     RT_VARIANT_PERSISTENT = 2,  /* persistent warps fetching pixels with warp-aggregated atomics */
     RT_VARIANT_WAVEFRONT = 3,   /* generate / extend / shade kernels over compacted ray queues */
+    RT_VARIANT_SAMPLES = 5,     /* primary stage -> the samples of each hit pixel evaluated in parallel (LCG jump-ahead,
+                                   speculative start offsets) -> per-pixel chain; falls back to sequential samples on the
+                                   device when most primary rays hit */
     RT_VARIANT_POOL = 4         /* persistent CTAs, K rays per lane pooled in shared memory, extend / leaf / shade
                                    stages picked by warp vote, top of the tree staged in shared memory */
 };

@@ -8,6 +8,7 @@
 #include <algorithm>
 #include <cstdarg>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <limits>
 #include <string>
@@ -22,6 +23,10 @@ cudaError_t rtLaunchPixel(const PassParams& P, bool count, bool ids, cudaStream_
 cudaError_t rtLaunchPersistent(const PassParams& P, bool count, bool ids, int sms, cudaStream_t stream);
 cudaError_t rtLaunchPool(const PassParams& P, bool count, bool ids, int sms, cudaStream_t stream);
 cudaError_t rtLaunchWavefront(const PassParams& P, bool count, bool ids, int sms, cudaStream_t stream);
+cudaError_t rtLaunchSamples(const PassParams& P, bool ids, int sms, uint32_t* todoA, uint32_t* todoB, cudaStream_t stream);
+int rtSpecRounds();
+cudaError_t rtSpecInit();
+int rtSpecTableK(int raysPerPixel, int nBounces);
 cudaError_t rtLaunchToRgba8(const float4* src, uchar4* dst, size_t n, cudaStream_t stream);
 cudaError_t rtLaunchBandCopy(float4* target, float4* dense, int width, int rows, int tileSizeY, int numTilesY,
                              int tile, int toDense, cudaStream_t stream);
@@ -60,6 +65,16 @@ struct rt_ctx {
     uint4* dQueueWork = nullptr;
     unsigned int* dQueueCount = nullptr;
     size_t queueCapacity = 0;
+    // samples variant: three more record planes and the table of F(k)
+    float4* dQueueC = nullptr;
+    float4* dQueueD = nullptr;
+    float4* dQueueE = nullptr;
+    float4* dSpecBuf = nullptr;
+    size_t specRecords = 0, specBufEntries = 0;
+    unsigned int* dWorkArr = nullptr;     // work counters of the rounds + todo counts
+    uint32_t* dTodo[2] = {nullptr, nullptr};
+    uint32_t* dChainK = nullptr;
+    float4* dChainColor = nullptr;
 };
 
 namespace {
@@ -113,8 +128,51 @@ void freeScene(rt_ctx* c) {
 
 void freeQueue(rt_ctx* c) {
     cudaFree(c->dQueueA); cudaFree(c->dQueueB); cudaFree(c->dQueuePix); cudaFree(c->dQueueWork);
+    cudaFree(c->dQueueC); cudaFree(c->dQueueD); cudaFree(c->dQueueE); cudaFree(c->dSpecBuf);
+    cudaFree(c->dTodo[0]); cudaFree(c->dTodo[1]); cudaFree(c->dChainK); cudaFree(c->dChainColor);
+    c->dTodo[0] = c->dTodo[1] = nullptr; c->dChainK = nullptr; c->dChainColor = nullptr;
     c->dQueueA = c->dQueueB = nullptr; c->dQueuePix = nullptr; c->dQueueWork = nullptr;
-    c->queueCapacity = 0;
+    c->dQueueC = c->dQueueD = c->dQueueE = c->dSpecBuf = nullptr;
+    c->queueCapacity = 0; c->specRecords = 0; c->specBufEntries = 0;
+}
+
+cudaError_t ensureQueue(rt_ctx* c, bool withWork);
+
+// Samples variant: record planes for every pixel of the target, and a table of K entries for up to half of the
+// pixels this pass owns (the speculative mode is only entered when at most half of them were queued).
+cudaError_t ensureSpec(rt_ctx* c, size_t ownedPixels, int K, uint32_t* capacityOut) {
+    cudaError_t e = ensureQueue(c, false);
+    if (e != cudaSuccess) return e;
+    if (c->specRecords < c->queueCapacity) {
+        cudaFree(c->dQueueC); cudaFree(c->dQueueD); cudaFree(c->dQueueE);
+        cudaFree(c->dTodo[0]); cudaFree(c->dTodo[1]); cudaFree(c->dChainK); cudaFree(c->dChainColor);
+        c->dQueueC = c->dQueueD = c->dQueueE = nullptr; c->specRecords = 0;
+        c->dTodo[0] = c->dTodo[1] = nullptr; c->dChainK = nullptr; c->dChainColor = nullptr;
+        if ((e = cudaMalloc(&c->dTodo[0], c->queueCapacity * sizeof(uint32_t))) != cudaSuccess) return e;
+        if ((e = cudaMalloc(&c->dTodo[1], c->queueCapacity * sizeof(uint32_t))) != cudaSuccess) return e;
+        if ((e = cudaMalloc(&c->dChainK, c->queueCapacity * sizeof(uint32_t))) != cudaSuccess) return e;
+        if ((e = cudaMalloc(&c->dChainColor, c->queueCapacity * sizeof(float4))) != cudaSuccess) return e;
+        if ((e = cudaMalloc(&c->dQueueC, c->queueCapacity * sizeof(float4))) != cudaSuccess) return e;
+        if ((e = cudaMalloc(&c->dQueueD, c->queueCapacity * sizeof(float4))) != cudaSuccess) return e;
+        if ((e = cudaMalloc(&c->dQueueE, c->queueCapacity * sizeof(float4))) != cudaSuccess) return e;
+        c->specRecords = c->queueCapacity;
+    }
+    // (test tooling: RT_VOTE_TUNE=..,..,1 forces the speculative mode, which then needs room for every pixel)
+    int t0 = 0, t1 = 0, t2 = 0;
+    if (const char* v = getenv("RT_VOTE_TUNE")) sscanf(v, "%d,%d,%d", &t0, &t1, &t2);
+    const size_t cap = t2 == 1 ? ownedPixels : (ownedPixels + 1) / 2;
+    const size_t need = std::max<size_t>(cap * size_t(std::max(K, 0)), 1);
+    if (c->specBufEntries < need) {
+        cudaFree(c->dSpecBuf); c->dSpecBuf = nullptr; c->specBufEntries = 0;
+        if ((e = cudaMalloc(&c->dSpecBuf, need * sizeof(float4))) != cudaSuccess) {
+            cudaGetLastError();
+            *capacityOut = 0;          // no room for the table: stage 3 evaluates every sample on demand
+            return cudaSuccess;
+        }
+        c->specBufEntries = need;
+    }
+    *capacityOut = uint32_t(std::min<size_t>(K > 0 ? c->specBufEntries / size_t(K) : 0, 0xffffffffu));
+    return cudaSuccess;
 }
 
 // The queue can hold every pixel of the target (all primary rays may hit); the work array only exists once a
@@ -175,7 +233,8 @@ int rt_create(rt_ctx** out, int device) {
         cudaEventCreate(&c->ev0) != cudaSuccess || cudaEventCreate(&c->ev1) != cudaSuccess ||
         cudaMalloc(&c->dCounters, RT_CNT_COUNT * sizeof(unsigned long long)) != cudaSuccess ||
         cudaMalloc(&c->dWork, sizeof(unsigned int)) != cudaSuccess ||
-        cudaMalloc(&c->dQueueCount, sizeof(unsigned int)) != cudaSuccess) {
+        cudaMalloc(&c->dQueueCount, sizeof(unsigned int)) != cudaSuccess ||
+        cudaMalloc(&c->dWorkArr, 64 * sizeof(unsigned int)) != cudaSuccess || rtSpecInit() != cudaSuccess) {
         delete c;
         return RT_ERR_CUDA;
     }
@@ -191,7 +250,7 @@ void rt_destroy(rt_ctx* c) {
     cudaStreamSynchronize(c->stream);
     freeScene(c);
     freeTargets(c);
-    cudaFree(c->dCounters); cudaFree(c->dWork); cudaFree(c->dQueueCount);
+    cudaFree(c->dCounters); cudaFree(c->dWork); cudaFree(c->dQueueCount); cudaFree(c->dWorkArr);
     if (c->ev0) cudaEventDestroy(c->ev0);
     if (c->ev1) cudaEventDestroy(c->ev1);
     if (c->ownStream) cudaStreamDestroy(c->ownStream);
@@ -395,7 +454,7 @@ int rt_set_params(rt_ctx* c, const rt_params* p) {
 
 int rt_set_variant(rt_ctx* c, int variant) {
     if (!c) return RT_ERR_INVALID;
-    if (variant < RT_VARIANT_AUTO || variant > RT_VARIANT_POOL) return fail(c, RT_ERR_INVALID, "unknown variant %d", variant);
+    if (variant < RT_VARIANT_AUTO || variant > RT_VARIANT_SAMPLES) return fail(c, RT_ERR_INVALID, "unknown variant %d", variant);
     c->variant = variant;
     return RT_OK;
 }
@@ -478,9 +537,22 @@ int renderPass(rt_ctx* c, int frameNumber, int tileX, int tileY, int flags, int 
     // AUTO, by measurement on B200 (profiles/r01_variants.md): many samples per pixel make the per-pixel work
     // uneven (sky pixels finish at once, surface pixels run rays_per_pixel paths) and the persistent warp-vote
     // kernel wins; otherwise the one-thread-per-pixel kernel does
-    if (variant == RT_VARIANT_AUTO) variant = u.rays_per_pixel >= 16 ? RT_VARIANT_PERSISTENT : RT_VARIANT_PIXEL;
+    if (variant == RT_VARIANT_AUTO) variant = u.rays_per_pixel >= 16 ? RT_VARIANT_SAMPLES : RT_VARIANT_PIXEL;
+    // the samples variant evaluates paths the reference would not (speculation): it has no counting instantiation
+    if (variant == RT_VARIANT_SAMPLES && (P.counters != nullptr || c->width > 65535 || c->height > 65535))
+        variant = RT_VARIANT_PERSISTENT;
     if (variant == RT_VARIANT_WAVEFRONT && (c->width > 65535 || c->height > 65535)) variant = RT_VARIANT_PIXEL;
-    if (variant == RT_VARIANT_WAVEFRONT) {
+    if (variant == RT_VARIANT_SAMPLES) {
+        const int K = rtSpecTableK(u.rays_per_pixel, u.nBounces);
+        uint32_t capacity = 0;
+        e = ensureSpec(c, size_t(P.ownedW) * size_t(P.ownedH), K, &capacity);
+        if (e != cudaSuccess) return fail(c, RT_ERR_NOMEM, "samples queue: %s", cudaGetErrorString(e));
+        P.queueA = c->dQueueA; P.queueB = c->dQueueB; P.queueC = c->dQueueC; P.queueD = c->dQueueD; P.queueE = c->dQueueE;
+        P.queueCount = c->dQueueCount; P.specBuf = c->dSpecBuf; P.specK = K; P.specCapacity = capacity;
+        P.specBufEntries = uint32_t(std::min<size_t>(c->specBufEntries, 0xffffffffu));
+        P.workCounters = c->dWorkArr; P.todoCount = c->dWorkArr + 32; P.chainK = c->dChainK; P.chainColor = c->dChainColor;
+        e = rtLaunchSamples(P, P.primaryIds != nullptr, c->smCount, c->dTodo[0], c->dTodo[1], c->stream);
+    } else if (variant == RT_VARIANT_WAVEFRONT) {
         e = ensureQueue(c, P.counters != nullptr);
         if (e != cudaSuccess) return fail(c, RT_ERR_NOMEM, "wavefront queue: %s", cudaGetErrorString(e));
         P.queueA = c->dQueueA; P.queueB = c->dQueueB; P.queuePix = c->dQueuePix; P.queueWork = c->dQueueWork;

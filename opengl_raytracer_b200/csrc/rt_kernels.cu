@@ -16,6 +16,7 @@
 #include "rt_vote.cuh"
 #include "rt_pool.cuh"
 #include "rt_wave.cuh"
+#include "rt_spec.cuh"
 
 namespace {
 
@@ -315,6 +316,65 @@ cudaError_t rtLaunchWavefront(const PassParams& P, bool count, bool ids, int sms
     else RT_LAUNCH2(false);
 #undef RT_LAUNCH2
     return cudaGetLastError();
+}
+
+// ---- SAMPLES variant: primary stage -> queue -> rounds of [parallel evaluation of F(k) -> chain]
+int rtSpecTableK(int raysPerPixel, int nBounces) { (void)nBounces; return spec::tableK(raysPerPixel); }
+int rtSpecRounds() { return spec::kRounds; }
+
+cudaError_t rtSpecInit() {
+    static uint2 lo[spec::kJumpLo], hi[spec::kJumpHi];
+    spec::fillJumpTables(lo, hi);
+    cudaError_t e = cudaMemcpyToSymbol(spec::cJumpLo, lo, sizeof lo);
+    if (e != cudaSuccess) return e;
+    return cudaMemcpyToSymbol(spec::cJumpHi, hi, sizeof hi);
+}
+
+cudaError_t rtLaunchSamples(const PassParams& Pin, bool ids, int sms, uint32_t* todoA, uint32_t* todoB, cudaStream_t stream) {
+    PassParams P = Pin;
+    if (P.ownedW <= 0 || P.ownedH <= 0) return cudaSuccess;
+    if (const char* e = getenv("RT_VOTE_TUNE")) sscanf(e, "%d,%d,%d", &P.tune[0], &P.tune[1], &P.tune[2]);
+    cudaError_t e = cudaMemsetAsync(P.workCounters, 0, 2 * spec::kRounds * sizeof(unsigned int), stream);
+    if (e != cudaSuccess) return e;
+    if ((e = cudaMemsetAsync(P.todoCount, 0, (spec::kRounds + 1) * sizeof(unsigned int), stream)) != cudaSuccess) return e;
+    if ((e = cudaMemsetAsync(P.queueCount, 0, sizeof(unsigned int), stream)) != cudaSuccess) return e;
+    const size_t smem = spec::smemBytes(P.scene.stackDepth);
+    const size_t smemEval = vote::smemBytes(P.scene.stackDepth);
+    dim3 grid((P.ownedW + 15) / 16, (P.ownedH + 7) / 8);
+    if (smem > 48 * 1024) {
+        cudaFuncSetAttribute(spec::rtSpecPrimaryKernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem));
+        cudaFuncSetAttribute(spec::rtSpecPrimaryKernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem));
+        cudaFuncSetAttribute(spec::rtSpecChainKernel, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem));
+    }
+    if (smemEval > 48 * 1024)
+        cudaFuncSetAttribute(spec::rtSpecEvalKernel, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smemEval));
+    if (ids) spec::rtSpecPrimaryKernel<true><<<grid, spec::kThreads, smem, stream>>>(P);
+    else spec::rtSpecPrimaryKernel<false><<<grid, spec::kThreads, smem, stream>>>(P);
+    if ((e = cudaGetLastError()) != cudaSuccess) return e;
+    if (P.nBounces <= 1 || P.raysPerPixel <= 0) return cudaSuccess;   // nothing was queued
+    const long long pixels = (long long)P.ownedW * P.ownedH;
+    int perSmEval = 0, perSmChain = 0;
+    if ((e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSmEval, spec::rtSpecEvalKernel, spec::kThreads, smemEval)) != cudaSuccess) return e;
+    if ((e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSmChain, spec::rtSpecChainKernel, spec::kThreads, smem)) != cudaSuccess) return e;
+    const long long wantEval = (pixels / 2 * std::max(P.specK, 1) + spec::kThreads - 1) / spec::kThreads;
+    const long long wantChain = (pixels + spec::kThreads - 1) / spec::kThreads;
+    const int gridEval = int(std::min<long long>((long long)sms * std::max(perSmEval, 1), std::max<long long>(wantEval, 1)));
+    const int gridChain = int(std::min<long long>((long long)sms * std::max(perSmChain, 1), std::max<long long>(wantChain, 1)));
+    // the rounds are launched unconditionally: a round without pixels (or the whole speculation, when stage 1 found
+    // that most primary rays hit) is a kernel that reads one counter and returns
+    const int K0 = P.specK;
+    for (int round = 0; round < spec::kRounds; round++) {
+        P.specRound = round;
+        // round 0: rays_per_pixel * 1.25 offsets; then top-ups that double (a chain can run to rays_per_pixel * nBounces)
+        P.specK = round == 0 ? K0 : std::min(spec::kMaxK / 4, spec::laterK(P.raysPerPixel) << (round - 1));
+        P.todoIn = (round & 1) ? todoA : todoB;
+        P.todoOut = (round & 1) ? todoB : todoA;
+        if (P.specK > 0 && P.specCapacity > 0) spec::rtSpecEvalKernel<<<gridEval, spec::kThreads, smemEval, stream>>>(P);
+        spec::rtSpecChainKernel<<<gridChain, spec::kThreads, smem, stream>>>(P);
+        if ((e = cudaGetLastError()) != cudaSuccess) return e;
+        if (P.specK <= 0 || P.specCapacity == 0) break;
+    }
+    return cudaSuccess;
 }
 
 cudaError_t rtLaunchToRgba8(const float4* src, uchar4* dst, size_t n, cudaStream_t stream) {

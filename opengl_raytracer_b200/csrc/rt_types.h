@@ -86,6 +86,21 @@ struct PassParams {
     uint32_t* queuePix;             // px | py << 16
     uint4* queueWork;               // counting passes only: work of the primary ray
     unsigned int* queueCount;
+    // samples variant: three more record planes, the table of F(k) (specK entries per queued pixel) and a 2nd work counter
+    float4* queueC;
+    float4* queueD;
+    float4* queueE;
+    float4* specBuf;
+    int32_t specK;
+    uint32_t specCapacity;          // queued pixels the table has room for
+    uint32_t specBufEntries;        // float4 entries of specBuf
+    unsigned int* workCounters;     // 2 per round (evaluation, chain), zeroed per pass
+    unsigned int* todoCount;        // [rounds + 1] pixels whose chain left its table
+    const uint32_t* todoIn;         // this round's pixels (round > 0)
+    uint32_t* todoOut;              // next round's pixels
+    uint32_t* chainK;               // parked chain position per queued pixel
+    float4* chainColor;             // parked colour sum (xyz) and sample index (w)
+    int32_t specRound;
     int32_t tune[4];                // scheduling thresholds (0 = built-in default); bench tooling only
     int32_t topCount;               // persistent variant: nodes [0, topCount) are staged in shared memory
 };

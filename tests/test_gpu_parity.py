@@ -9,7 +9,7 @@ from opengl_raytracer_b200 import rtlib
 
 pytestmark = pytest.mark.gpu
 
-VARIANTS = ["pixel", "persistent", "pool", "wavefront"]
+VARIANTS = ["pixel", "persistent", "pool", "wavefront", "samples"]
 EXACT_COUNTERS = ("rays", "internal", "leaves", "tri_tests", "hits", "pops", "paths")
 
 
@@ -73,6 +73,31 @@ def test_image_ids_counters_match_oracle(ctx, oracle_mod, scene_buffers, scene, 
     assert {k: cnt[k] for k in EXACT_COUNTERS} == want
     assert cnt["rays_traced"] == cnt["rays"] - (spp - 1) * w * h * frames * (1 if params.nBounces > 0 else 0)
     assert np.array_equal(ctx.read_rgba8(), oracle_mod.to_rgba8(acc))
+
+
+@pytest.mark.parametrize("mode", ["0,0,0", "0,0,1", "0,0,2"], ids=["auto", "speculative", "sequential"])
+@pytest.mark.parametrize("scene,w,h,spp,frames,over", [
+    ("rects_box", 96, 54, 5, 2, {}),                      # closed room: forced speculation leaves its table -> on-demand tail
+    ("rects_box", 64, 36, 3, 1, {"lambertian": False, "sky_brightness": 0.5}),
+    ("rects_box", 64, 36, 4, 1, {"bounces": 0}),          # every path ends at bounce 0
+    ("cfg1_open", 160, 90, 4, 2, {}),
+    ("cfg4_open", 192, 108, 24, 1, {}),                   # open sky: the case the variant is for
+    ("cfg2_box", 96, 54, 3, 1, {}),                       # emitter + mirror sphere
+])
+def test_samples_variant_matches_oracle(ctx, oracle_mod, scene_buffers, monkeypatch, scene, w, h, spp, frames, over, mode):
+    """The samples variant (parallel evaluation of F(k) + per-pixel chain) without counting flags, in its device-chosen
+    mode and with either mode forced: RGBA32F bit-exact against the oracle, primary ids exact."""
+    monkeypatch.setenv("RT_VOTE_TUNE", mode)
+    tris, boxes, indices, cfg = scene_buffers(scene)
+    params = cfg.scaled(w, h, spp).params(**over)
+    got = _render_gpu(ctx, tris, boxes, indices, params, frames, "samples", flags=rtlib.PASS_PRIMARY_IDS)
+    ids = ctx.read_primary_ids()
+    acc = None
+    for frame in range(frames):
+        acc, ref_ids, _ = oracle_mod.render_pass(tris, boxes, indices, params.replace(frameNumber=frame), prev=acc,
+                                                 want_ids=True)
+    assert np.array_equal(ids, ref_ids)
+    assert got.tobytes() == acc.tobytes(), f"{(got != acc).any(-1).sum()} pixels differ"
 
 
 @pytest.mark.parametrize("variant", VARIANTS)
