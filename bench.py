@@ -278,7 +278,7 @@ def run_gpu(args):
         res = {"cfg": cfg, "counters": total, "ms_per_step": ms_step, "kernel_ms": kernel_ms,
                "mrays_s": total["rays_traced"] / (ms_step * 1e-3) / 1e6,
                "ref_equiv_mrays_s": total["rays"] / (ms_step * 1e-3) / 1e6, "clocks": clocks,
-               "local_alg_bytes": local_alg_bytes, "launches": steps}
+               "local_alg_bytes": local_alg_bytes, "launches": steps}   # traversal-kernel passes; the caller multiplies by kernels per pass
         if with_e2e:
             # end to end through the C ABI with HOST buffers: scene upload (H2D), uniforms, draw, gather, and the
             # RGBA32F read-back (D2H) on rank 0, every step
@@ -311,16 +311,18 @@ def run_gpu(args):
     alg_bytes = main["local_alg_bytes"] + fb_bytes
     achieved = alg_bytes / (main["kernel_ms"] * 1e-3) / 1e9
     variant = args.variant
+    sm_count = torch.cuda.get_device_properties(dev).multi_processor_count
     if variant == "auto":
-        variant = "persistent" if cfg.rays_per_pixel >= 16 else "pixel"          # rt_api.cu renderPass()
+        owned = cfg.width * cfg.height // world                                   # rt_api.cu renderPass()
+        variant = "pixel" if cfg.rays_per_pixel < 16 else ("persistent" if owned > sm_count * 2048 * 16 else "samples")
     kernel = {"pixel": "rtPixelKernel", "persistent": "vote::rtVoteKernel", "pool": "pool::rtPoolKernel",
-              "wavefront": "wave::rtPrimaryKernel + wave::rtPathKernel"}[variant]
+              "wavefront": "wave::rtPrimaryKernel + wave::rtPathKernel",
+              "samples": "spec::rtSpecPrimaryKernel + rounds of spec::rtSpecEvalKernel / spec::rtSpecChainKernel"}[variant]
     prof = {}
     ppath = os.path.join(ROOT, "profiles", "bench_kernel_counters.json")
     if os.path.isfile(ppath):
         with open(ppath) as f:
             prof = json.load(f).get(f"{WORKLOAD}/{variant}", {})
-    sm_count = torch.cuda.get_device_properties(dev).multi_processor_count
     clock_mhz = (main["clocks"] or {}).get("sm_mhz") or sm_max
     roofline = {"bound": "hbm", "achieved": achieved, "peak": peak_gbs, "unit": "GB/s", "frac": achieved / peak_gbs,
                 "traffic": (prof["dram_bytes_per_launch"] / world) if prof.get("dram_bytes_per_launch") else None, "peak_source": peak_src, "kernel": kernel,
@@ -352,7 +354,11 @@ def run_gpu(args):
                        "ray_unit": "distinct rays traced: raycast() calls with the primary ray of a pixel-frame counted once, not once per sample"},
             "ms_per_frame": main["ms_per_step"], "rays_per_step": cnt["rays_traced"],
             "reference_equivalent": {"rays_per_step": cnt["rays"], "mrays_s": main["ref_equiv_mrays_s"]},
-            "e2e": main["e2e"], "gpu_launches": main["launches"], "roofline": roofline, "clocks": main["clocks"]}
+            "e2e": main["e2e"], "roofline": roofline, "clocks": main["clocks"],
+            # this repo's kernels launched by rank 0 inside the timed region: the pass (1 kernel; the samples variant
+            # launches its primary stage + 6 rounds of evaluation/chain kernels) + band gather (1) and scatters (N - 1)
+            "gpu_launches": main["launches"] * ((13 if variant == "samples" else 2 if variant == "wavefront" else 1)
+                                                + (world if world > 1 else 0))}
 
     if world == 1 and not args.no_cpu:
         line["cpu_baseline"] = cpu_baseline(args)

@@ -534,10 +534,17 @@ int renderPass(rt_ctx* c, int frameNumber, int tileX, int tileY, int flags, int 
     }
     cudaError_t e;
     int variant = c->variant;
-    // AUTO, by measurement on B200 (profiles/r01_variants.md): many samples per pixel make the per-pixel work
-    // uneven (sky pixels finish at once, surface pixels run rays_per_pixel paths) and the persistent warp-vote
-    // kernel wins; otherwise the one-thread-per-pixel kernel does
-    if (variant == RT_VARIANT_AUTO) variant = u.rays_per_pixel >= 16 ? RT_VARIANT_SAMPLES : RT_VARIANT_PIXEL;
+    // AUTO, by measurement on B200 (profiles/r01_variants.md).  Few samples per pixel: the one-thread-per-pixel
+    // kernel.  Many samples per pixel make the per-pixel work uneven (sky pixels finish at once, surface pixels run
+    // rays_per_pixel paths): the persistent warp-vote kernel, as long as this GPU owns enough pixels to stay
+    // throughput-bound; when its share of the frame is small (tile-sharded frame on several GPUs) the serial sample
+    // chain of a pixel bounds the pass and the samples variant, which evaluates the samples in parallel, wins
+    // (dragon 4K 64 spp, this GPU's share 1 / 1/2 / 1/4 / 1/8: persistent 27.3 / 16.5 / 14.0 / 12.5 ms, samples
+    // 31.9 / 16.6 / 9.2 / 5.2 ms).
+    if (variant == RT_VARIANT_AUTO) {
+        const long long owned = (long long)P.ownedW * P.ownedH, manyPixels = (long long)c->smCount * 2048 * 16;
+        variant = u.rays_per_pixel < 16 ? RT_VARIANT_PIXEL : (owned > manyPixels ? RT_VARIANT_PERSISTENT : RT_VARIANT_SAMPLES);
+    }
     // the samples variant evaluates paths the reference would not (speculation): it has no counting instantiation
     if (variant == RT_VARIANT_SAMPLES && (P.counters != nullptr || c->width > 65535 || c->height > 65535))
         variant = RT_VARIANT_PERSISTENT;

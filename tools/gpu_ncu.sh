@@ -14,7 +14,7 @@ if [ "${LIST:-0}" = "1" ]; then
 fi
 for V in ${VARIANTS:-pixel persistent pool}; do
   python tools/prof_case.py $CASE $V 2 > gpurun_out/plain_${V}_$TAG.log 2>&1 &&
-  ncu --set full --clock-control none --import-source on -k regex:'rt(Pixel|Vote|Pool)Kernel' -s 1 -c 1 -f -o gpurun_out/prof_${NAME}_${V}_$TAG \
+  ncu --set full --clock-control none --import-source on -k regex:'rt(Pixel|Vote|Pool|SpecEval)Kernel' -s 1 -c 1 -f -o gpurun_out/prof_${NAME}_${V}_$TAG \
       python tools/prof_case.py $CASE $V 2 > gpurun_out/ncu_${V}_$TAG.log 2>&1
   echo "ncu $V rc=$?"; tail -1 gpurun_out/ncu_${V}_$TAG.log
 done
