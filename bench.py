@@ -58,42 +58,61 @@ def algorithmic_bytes(cnt):
 
 
 class ClockSampler:
-    """nvidia-smi clocks / throttle reasons sampled during the timed region."""
-    FIELDS = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
-              "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
-              "clocks_event_reasons.sw_power_cap")
+    """SM clock / throttle reasons of this rank's GPU, sampled during the timed region.  NVML in-process (a thread,
+    started before the warm-up so that NVML's start-up cost stays outside the timed region; `mark()` drops what was
+    sampled before it) — forking nvidia-smi next to the timed loop stalled the launching thread for tens of ms."""
+    PERIOD = 0.05
 
     def __init__(self, index):
-        self.index, self.rows, self.proc = index, [], None
+        self.index, self.rows, self.handle, self.nvml, self.running = index, [], None, None, False
 
     def start(self):
         try:
-            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.FIELDS}",
-                                          "--format=csv,noheader,nounits", "-lms", "200"],
-                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
-            threading.Thread(target=self._pump, daemon=True).start()
-        except OSError:
-            self.proc = None
+            import pynvml
+            pynvml.nvmlInit()
+            uuid = str(torch_uuid(self.index))
+            try:
+                self.handle = pynvml.nvmlDeviceGetHandleByUUID(("GPU-" + uuid) if not uuid.startswith("GPU-") else uuid)
+            except Exception:
+                self.handle = pynvml.nvmlDeviceGetHandleByIndex(self.index)
+            self.nvml, self.running = pynvml, True
+            self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(self.handle, pynvml.NVML_CLOCK_SM)
+            self.thread = threading.Thread(target=self._pump, daemon=True)
+            self.thread.start()
+        except Exception as e:                                     # no NVML: clocks are reported as unknown
+            sys.stderr.write(f"clock sampling unavailable: {e}\n")
+            self.nvml = None
 
     def _pump(self):
-        for line in self.proc.stdout:
-            self.rows.append([c.strip() for c in line.split(",")])
+        n = self.nvml
+        while self.running:
+            try:
+                self.rows.append((n.nvmlDeviceGetClockInfo(self.handle, n.NVML_CLOCK_SM),
+                                  n.nvmlDeviceGetCurrentClocksEventReasons(self.handle)))
+            except Exception:
+                pass
+            time.sleep(self.PERIOD)
+
+    def mark(self):
+        self.rows = []
 
     def stop(self):
-        if self.proc:
-            self.proc.terminate()
-        sm, mx, reasons = [], [], set()
-        names = ("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap")
-        for r in self.rows:
-            try:
-                sm.append(float(r[0])); mx.append(float(r[1]))
-            except (ValueError, IndexError):
-                continue
-            for name, v in zip(names, r[3:7]):
-                if v.lower().startswith("active"):
-                    reasons.add(name)
-        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
-                "reasons": sorted(reasons), "samples": len(sm)}
+        if self.nvml is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
+        self.running = False
+        self.thread.join()
+        n = self.nvml
+        bits = {"hw_slowdown": n.nvmlClocksEventReasonHwSlowdown, "hw_thermal_slowdown": n.nvmlClocksEventReasonHwThermalSlowdown,
+                "sw_thermal_slowdown": n.nvmlClocksEventReasonSwThermalSlowdown, "sw_power_cap": n.nvmlClocksEventReasonSwPowerCap}
+        sm = [r[0] for r in self.rows]
+        reasons = sorted(name for name, bit in bits.items() if any(r[1] & bit for r in self.rows))
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": float(self.max_mhz),
+                "reasons": reasons, "samples": len(sm)}
+
+
+def torch_uuid(index):
+    import torch
+    return torch.cuda.get_device_properties(index).uuid
 
 
 def build_scene(name):
@@ -242,13 +261,14 @@ def run_gpu(args):
         local_alg_bytes = algorithmic_bytes(traced)
         ctx.set_params(params)
 
-        for _ in range(warmup):
-            step()
         sampler = ClockSampler(local)
         if rank == 0:
             sampler.start()
+        for _ in range(warmup):
+            step()
         kernel_events = []
         barrier()
+        sampler.mark()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record()
         for _ in range(steps):
@@ -259,26 +279,38 @@ def run_gpu(args):
             k0.record()
             ctx.render_pass(0, 0, rank, flags=rtlib.PASS_SKIP_MASKED)
             k1.record()
-            kernel_events.append((k0, k1))
             if world > 1:
                 rows = distributed.max_band_rows(cfg.height, BAND_ROWS, world)
                 if dense is None:
                     dense = torch.empty((rows, cfg.width, 4), dtype=torch.float32, device=dev)
                 ctx.band_gather(rank, dense.data_ptr())
+                k2 = torch.cuda.Event(enable_timing=True); k2.record()
                 bufs = distributed.gather_bands(dist, dense, rank, world)
+                k3 = torch.cuda.Event(enable_timing=True); k3.record()
                 if rank == 0:
                     for g in range(1, world):
                         ctx.band_scatter(g, bufs[g].data_ptr())
+                k4 = torch.cuda.Event(enable_timing=True); k4.record()
+                kernel_events.append((k0, k1, k2, k3, k4))
+            else:
+                kernel_events.append((k0, k1))
         e1.record()
         barrier()
         clocks = sampler.stop() if rank == 0 else None
         ms_total = max_over_ranks(e0.elapsed_time(e1))
-        kernel_ms = float(np.mean([a.elapsed_time(b) for a, b in kernel_events]))
+        kernel_ms = float(np.mean([ev[0].elapsed_time(ev[1]) for ev in kernel_events]))
+        phases = None
+        if world > 1:
+            # where a multi-GPU step goes: slowest rank's pass, then pack / NCCL gather (includes waiting for the slowest
+            # rank) / scatter as seen by rank 0
+            mine = [float(np.mean([ev[i].elapsed_time(ev[i + 1]) for ev in kernel_events])) for i in range(4)]
+            phases = {"pass_max_over_ranks": max_over_ranks(mine[0]), "pass_rank0": mine[0], "pack_rank0": mine[1],
+                      "nccl_gather_rank0": mine[2], "scatter_rank0": mine[3]}
         ms_step = ms_total / steps
         res = {"cfg": cfg, "counters": total, "ms_per_step": ms_step, "kernel_ms": kernel_ms,
                "mrays_s": total["rays_traced"] / (ms_step * 1e-3) / 1e6,
                "ref_equiv_mrays_s": total["rays"] / (ms_step * 1e-3) / 1e6, "clocks": clocks,
-               "local_alg_bytes": local_alg_bytes, "launches": steps}   # traversal-kernel passes; the caller multiplies by kernels per pass
+               "local_alg_bytes": local_alg_bytes, "launches": steps, "phases_ms": phases}   # traversal-kernel passes; the caller multiplies by kernels per pass
         if with_e2e:
             # end to end through the C ABI with HOST buffers: scene upload (H2D), uniforms, draw, gather, and the
             # RGBA32F read-back (D2H) on rank 0, every step
@@ -354,7 +386,7 @@ def run_gpu(args):
                        "ray_unit": "distinct rays traced: raycast() calls with the primary ray of a pixel-frame counted once, not once per sample"},
             "ms_per_frame": main["ms_per_step"], "rays_per_step": cnt["rays_traced"],
             "reference_equivalent": {"rays_per_step": cnt["rays"], "mrays_s": main["ref_equiv_mrays_s"]},
-            "e2e": main["e2e"], "roofline": roofline, "clocks": main["clocks"],
+            "e2e": main["e2e"], "roofline": roofline, "clocks": main["clocks"], "phases_ms": main["phases_ms"],
             # this repo's kernels launched by rank 0 inside the timed region: the pass (1 kernel; the samples variant
             # launches its primary stage + 6 rounds of evaluation/chain kernels) + band gather (1) and scatters (N - 1)
             "gpu_launches": main["launches"] * ((13 if variant == "samples" else 2 if variant == "wavefront" else 1)

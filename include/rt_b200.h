@@ -130,6 +130,7 @@ int rt_render_frames_sum(rt_ctx* ctx, int first_frame, int n_frames, int frame_s
 
 /* Read-backs of the current accumulation target (the one the last pass wrote). */
 int rt_read_accum_f32(rt_ctx* ctx, float* dst_rgba);        /* width*height*4 floats */
+int rt_write_accum_f32(rt_ctx* ctx, const float* src_rgba); /* checkpoint restore into the current target */
 int rt_read_rgba8(rt_ctx* ctx, uint8_t* dst_rgba);          /* round(clamp(x,0,1)*255), main.py:434 */
 int rt_read_primary_ids(rt_ctx* ctx, int32_t* dst);         /* width*height, needs RT_PASS_PRIMARY_IDS */
 int rt_read_counters(rt_ctx* ctx, uint64_t* dst, int n);    /* RT_CNT_* since rt_reset_counters */

@@ -638,6 +638,18 @@ int rt_read_accum_f32(rt_ctx* c, float* dst) {
     return RT_OK;
 }
 
+// Upload an accumulation image into the current target (checkpoint restore; the GL counterpart would be
+// glTexSubImage2D on accum_tex[accum_index], which the reference never does).
+int rt_write_accum_f32(rt_ctx* c, const float* src) {
+    if (!c || !src) return RT_ERR_INVALID;
+    if (!c->target[0]) return fail(c, RT_ERR_STATE, "no target");
+    Bind bind(c);
+    RT_CUDA(c, cudaMemcpyAsync(c->target[c->accumIndex], src, size_t(c->width) * c->height * sizeof(float4),
+                               cudaMemcpyHostToDevice, c->stream));
+    RT_CUDA(c, cudaStreamSynchronize(c->stream));
+    return RT_OK;
+}
+
 int rt_read_rgba8(rt_ctx* c, uint8_t* dst) {
     if (!c || !dst) return RT_ERR_INVALID;
     if (!c->target[0]) return fail(c, RT_ERR_STATE, "no target");

@@ -89,6 +89,7 @@ def load_library(path: str | None = None):
         "rt_render_frames": (i, [vp, i, i]),
         "rt_render_frames_sum": (i, [vp, i, i, i]),
         "rt_read_accum_f32": (i, [vp, vp]),
+        "rt_write_accum_f32": (i, [vp, vp]),
         "rt_read_rgba8": (i, [vp, vp]),
         "rt_read_primary_ids": (i, [vp, vp]),
         "rt_read_counters": (i, [vp, vp, i]),
@@ -228,6 +229,13 @@ class Context:
             out = np.empty((self.height, self.width, 4), dtype=np.float32)
         self._check(self.lib.rt_read_accum_f32(self.handle, out.ctypes.data))
         return out
+
+    def write_accum_f32(self, image: np.ndarray):
+        """Upload an (H, W, 4) float32 accumulation into the current target (checkpoint restore)."""
+        image = np.ascontiguousarray(image, dtype=np.float32)
+        if image.shape != (self.height, self.width, 4):
+            raise ValueError(f"accumulation must be {(self.height, self.width, 4)}, got {image.shape}")
+        self._check(self.lib.rt_write_accum_f32(self.handle, image.ctypes.data))
 
     def read_rgba8(self, out: np.ndarray | None = None) -> np.ndarray:
         if out is None:

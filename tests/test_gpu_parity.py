@@ -242,3 +242,39 @@ def test_full_size_band_against_oracle(ctx, oracle_mod, scene_buffers):
     want, _, _ = oracle_mod.render_pass(tris, boxes, indices, band)
     rows = slice(17 * 16, 18 * 16)
     assert got[rows].tobytes() == want[rows].tobytes()
+
+
+def test_headless_app_loop_and_checkpoint(tmp_path, oracle_mod):
+    """The headless App (main.py's loop without a window): tile/frame sequencing equals the oracle's frame loop, and a
+    run interrupted by save_checkpoint / load_checkpoint continues bit-identically."""
+    from opengl_raytracer_b200 import configs
+    from opengl_raytracer_b200.app import App
+    from opengl_raytracer_b200.scene import Scene
+    cfg = configs.scene_configs()["rects_box"]
+    objs = lambda: configs.build_objects(cfg.objects)
+    tris, boxes, indices = Scene(objs()).pack()
+    app = App((96, 54), (96, 54), bounces=3, rays_per_pixel=2, tileSize=2, objects=objs(), cam_pos=cfg.cam_pos,
+              cam_dir=cfg.cam_dir)
+    assert app.params.nBounces == 4 and app.params.numTilesX == 2 and app.params.numTilesY == 2
+    app.main(frames=3)
+    assert app.screen.frame_count == 3 and app.total_frames == 12
+    whole = app.screen.read_accum()
+    want = oracle_mod.render_frames(tris, boxes, indices, app.params, 0, 3)
+    assert whole.tobytes() == want.tobytes()
+    # interrupted run: 1 frame + 1 extra pass, checkpoint, fresh app, resume
+    app.resetFrames()
+    assert app.screen.frame_count == 0 and not app.screen.read_accum().any()
+    app.main(frames=1)
+    app.step()
+    ck = str(tmp_path / "ck.npz")
+    app.save_checkpoint(ck)
+    app.close()
+    app2 = App((96, 54), (96, 54), bounces=3, rays_per_pixel=2, tileSize=2, objects=objs(), cam_pos=cfg.cam_pos,
+               cam_dir=cfg.cam_dir)
+    app2.load_checkpoint(ck)
+    assert (app2.screen.frame_count, app2.tileX, app2.tileY) == (1, 1, 0)
+    app2.main(frames=2)                     # finishes frame 1, then frame 2
+    assert app2.screen.frame_count == 3
+    assert app2.screen.read_accum().tobytes() == whole.tobytes()
+    app2.save(str(tmp_path / "out.png"))
+    app2.close()
