@@ -264,48 +264,60 @@ def run_gpu(args):
         sampler = ClockSampler(local)
         if rank == 0:
             sampler.start()
-        for _ in range(warmup):
-            step()
         kernel_events = []
-        barrier()
-        sampler.mark()
-        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        e0.record()
-        for _ in range(steps):
+
+        def timed_step():
+            """One step exactly as timed (the warm-up runs the same body, so that lazily loaded kernels, NCCL
+            channels and allocator blocks are all in place before the clock starts)."""
+            nonlocal dense
+            ev = [torch.cuda.Event(enable_timing=True) for _ in range(6 if world > 1 else 3)]
+            ev[0].record()
             flush_buf.zero_()                                   # L2 flush between steps (inside the timed region)
             ctx.target_clear()
             ctx.set_params(distributed.band_params(params, rank, world, BAND_ROWS))
-            k0, k1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-            k0.record()
+            ev[1].record()
             ctx.render_pass(0, 0, rank, flags=rtlib.PASS_SKIP_MASKED)
-            k1.record()
+            ev[2].record()
             if world > 1:
                 rows = distributed.max_band_rows(cfg.height, BAND_ROWS, world)
                 if dense is None:
                     dense = torch.empty((rows, cfg.width, 4), dtype=torch.float32, device=dev)
                 ctx.band_gather(rank, dense.data_ptr())
-                k2 = torch.cuda.Event(enable_timing=True); k2.record()
+                ev[3].record()
                 bufs = distributed.gather_bands(dist, dense, rank, world)
-                k3 = torch.cuda.Event(enable_timing=True); k3.record()
+                ev[4].record()
                 if rank == 0:
                     for g in range(1, world):
                         ctx.band_scatter(g, bufs[g].data_ptr())
-                k4 = torch.cuda.Event(enable_timing=True); k4.record()
-                kernel_events.append((k0, k1, k2, k3, k4))
-            else:
-                kernel_events.append((k0, k1))
+                ev[5].record()
+            kernel_events.append(ev)
+
+        for _ in range(warmup):
+            timed_step()
+        kernel_events.clear()
+        barrier()
+        sampler.mark()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(steps):
+            timed_step()
         e1.record()
         barrier()
         clocks = sampler.stop() if rank == 0 else None
         ms_total = max_over_ranks(e0.elapsed_time(e1))
-        kernel_ms = float(np.mean([ev[0].elapsed_time(ev[1]) for ev in kernel_events]))
-        phases = None
+        def phase(i):
+            return float(np.mean([ev[i].elapsed_time(ev[i + 1]) for ev in kernel_events]))
+
+        kernel_ms = phase(1)
+        phases = {"flush_and_clear": phase(0), "pass": kernel_ms}
+        if os.environ.get("RT_BENCH_TRACE"):
+            for ev in kernel_events:
+                sys.stderr.write(f"rank {rank} step phases ms: " + " ".join(f"{a.elapsed_time(b):.3f}" for a, b in zip(ev, ev[1:])) + "\n")
         if world > 1:
-            # where a multi-GPU step goes: slowest rank's pass, then pack / NCCL gather (includes waiting for the slowest
-            # rank) / scatter as seen by rank 0
-            mine = [float(np.mean([ev[i].elapsed_time(ev[i + 1]) for ev in kernel_events])) for i in range(4)]
-            phases = {"pass_max_over_ranks": max_over_ranks(mine[0]), "pass_rank0": mine[0], "pack_rank0": mine[1],
-                      "nccl_gather_rank0": mine[2], "scatter_rank0": mine[3]}
+            # where a multi-GPU step goes: slowest rank's pass, then pack / NCCL gather (includes waiting for the
+            # slowest rank) / scatter; rank 0's view
+            phases.update({"pass_max_over_ranks": max_over_ranks(kernel_ms), "pack": phase(2), "nccl_gather": phase(3),
+                           "scatter": phase(4)})
         ms_step = ms_total / steps
         res = {"cfg": cfg, "counters": total, "ms_per_step": ms_step, "kernel_ms": kernel_ms,
                "mrays_s": total["rays_traced"] / (ms_step * 1e-3) / 1e6,

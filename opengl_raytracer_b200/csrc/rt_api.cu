@@ -12,6 +12,7 @@
 #include <cstring>
 #include <limits>
 #include <string>
+#include <type_traits>
 #include <vector>
 
 #include "../../include/rt_b200.h"
@@ -31,6 +32,8 @@ cudaError_t rtLaunchToRgba8(const float4* src, uchar4* dst, size_t n, cudaStream
 cudaError_t rtLaunchBandCopy(float4* target, float4* dense, int width, int rows, int tileSizeY, int numTilesY,
                              int tile, int toDense, cudaStream_t stream);
 cudaError_t rtLaunchFinishSum(float4* target, size_t n, float frames, cudaStream_t stream);
+cudaError_t rtLaunchBuildRecords(const float4* raw, const uint32_t* triId, uint32_t nSlots, TriRec* tris, ShadeRec* shade,
+                                 cudaStream_t stream);
 
 struct rt_ctx {
     int device = 0;
@@ -44,6 +47,10 @@ struct rt_ctx {
     ShadeRec* dShade = nullptr;
     uint32_t* dTriId = nullptr;
     uint2* dBig = nullptr;
+    float4* dRawTris = nullptr;           // the caller's tris[] as uploaded (144 B each); records are built from it on the device
+    size_t capNodes = 0, capSlots = 0, capSlotRecs = 0, capBig = 0, capRaw = 0;   // element capacities: re-uploads reuse the buffers
+    void* hStage = nullptr;               // pinned staging for nodes + slot ids + big leaves
+    size_t hStageBytes = 0;
     DeviceScene scene{};
     bool haveScene = false;
     // uniforms
@@ -121,7 +128,10 @@ static_assert(sizeof(HostTri) == 144 && sizeof(HostBox) == 48, "std430 layout");
 
 void freeScene(rt_ctx* c) {
     cudaFree(c->dNodes); cudaFree(c->dTris); cudaFree(c->dShade); cudaFree(c->dTriId); cudaFree(c->dBig);
+    cudaFree(c->dRawTris); cudaFreeHost(c->hStage);
     c->dNodes = nullptr; c->dTris = nullptr; c->dShade = nullptr; c->dTriId = nullptr; c->dBig = nullptr;
+    c->dRawTris = nullptr; c->hStage = nullptr;
+    c->capNodes = c->capSlots = c->capSlotRecs = c->capBig = c->capRaw = c->hStageBytes = 0;
     c->haveScene = false;
     c->scene = DeviceScene{};
 }
@@ -291,9 +301,7 @@ int rt_scene_upload(rt_ctx* c, const void* trisV, uint32_t nTris, const void* bo
     const HostBox* boxes = static_cast<const HostBox*>(boxesV);
 
     std::vector<NodeRec> nodes;
-    std::vector<TriRec> triRecs;
-    std::vector<ShadeRec> shadeRecs;
-    std::vector<uint32_t> triIds;
+    std::vector<uint32_t> triIds;                  // slot -> index into the caller's tris[]
     std::vector<uint2> bigLeaves;
     DeviceScene sc{};
     sc.rootRef = RT_REF_NONE;
@@ -347,31 +355,12 @@ int rt_scene_upload(rt_ctx* c, const void* trisV, uint32_t nTris, const void* bo
         // 2. numbering: internal nodes breadth-first, leaves in order of first reference
         std::vector<int32_t> ref(nBoxes, RT_REF_NONE);
         std::vector<uint32_t> order;
+        uint32_t nSlots = 0;
         auto leafRef = [&](uint32_t i) -> int32_t {
             const HostBox& b = boxes[i];
-            const uint32_t first = uint32_t(triRecs.size());
-            for (uint32_t k = 0; k < b.numTriangles; k++) {
-                const uint32_t id = indices[b.triangleOffset + k];
-                const HostTri& t = tris[id];
-                // fragment.glsl:112-116, same operation order, no contraction (-ffp-contract=off on the host)
-                volatile float abx = t.v1p[0] - t.v0p[0], aby = t.v1p[1] - t.v0p[1], abz = t.v1p[2] - t.v0p[2];
-                volatile float acx = t.v2p[0] - t.v0p[0], acy = t.v2p[1] - t.v0p[1], acz = t.v2p[2] - t.v0p[2];
-                volatile float m0 = aby * acz, m1 = acy * abz, m2 = abz * acx, m3 = acz * abx, m4 = abx * acy, m5 = acx * aby;
-                TriRec r;
-                r.v0x = t.v0p[0]; r.v0y = t.v0p[1]; r.v0z = t.v0p[2];
-                r.abx = abx; r.aby = aby; r.abz = abz; r.acx = acx; r.acy = acy; r.acz = acz;
-                r.nx = m0 - m1; r.ny = m2 - m3; r.nz = m4 - m5;
-                triRecs.push_back(r);
-                ShadeRec s{};
-                s.n0x = t.v0n[0]; s.n0y = t.v0n[1]; s.n0z = t.v0n[2];
-                s.n1x = t.v1n[0]; s.n1y = t.v1n[1]; s.n1z = t.v1n[2];
-                s.n2x = t.v2n[0]; s.n2y = t.v2n[1]; s.n2z = t.v2n[2];
-                s.colR = t.color[0]; s.colG = t.color[1]; s.colB = t.color[2];
-                s.emcR = t.emc[0]; s.emcG = t.emc[1]; s.emcB = t.emc[2];
-                s.emission = t.surface[0]; s.roughness = t.surface[1];
-                shadeRecs.push_back(s);
-                triIds.push_back(id);
-            }
+            const uint32_t first = nSlots;
+            triIds.insert(triIds.end(), indices + b.triangleOffset, indices + b.triangleOffset + b.numTriangles);
+            nSlots += b.numTriangles;
             uint32_t code;
             if (b.numTriangles <= RT_LEAF_MAX) {
                 code = (first << RT_LEAF_BITS) | b.numTriangles;
@@ -395,6 +384,7 @@ int rt_scene_upload(rt_ctx* c, const void* trisV, uint32_t nTris, const void* bo
         sc.rootRef = assign(0);
         for (int k = 0; k < 3; k++) { sc.rootMin[k] = boxes[0].posMin[k]; sc.rootMax[k] = boxes[0].posMax[k]; }
         nodes.reserve(nBoxes);
+        triIds.reserve(nIndices);
         for (size_t at = 0; at < order.size(); at++) {
             const HostBox& b = boxes[order[at]];
             NodeRec n{};
@@ -413,30 +403,58 @@ int rt_scene_upload(rt_ctx* c, const void* trisV, uint32_t nTris, const void* bo
                 n.bMinX = n.bMinY = n.bMinZ = n.bMaxX = n.bMaxY = n.bMaxZ = nan;
             }
             nodes.push_back(n);
-            if (triRecs.size() >= RT_MAX_SLOTS)
+            if (triIds.size() >= RT_MAX_SLOTS)
                 return fail(c, RT_ERR_INVALID, "scene needs more than %u triangle slots", RT_MAX_SLOTS);
         }
     }
 
-    cudaStreamSynchronize(c->stream);
-    freeScene(c);
-    auto upload = [&](auto** dst, const auto& vec) -> cudaError_t {
-        using T = typename std::remove_reference<decltype(vec)>::type::value_type;
-        const size_t bytes = std::max<size_t>(vec.size(), 1) * sizeof(T);
-        cudaError_t e = cudaMalloc(reinterpret_cast<void**>(dst), bytes);
-        if (e != cudaSuccess) return e;
-        if (!vec.empty()) e = cudaMemcpyAsync(*dst, vec.data(), vec.size() * sizeof(T), cudaMemcpyHostToDevice, c->stream);
+    // device side: buffers are reused while they are large enough (a re-upload then costs no allocation); the three small
+    // tables go through one pinned staging block, the caller's tris[] is copied as it is and the 48 B + 80 B records of
+    // every slot are built from it by a kernel (same operations, same order, no contraction: fragment.glsl:112-116)
+    RT_CUDA(c, cudaStreamSynchronize(c->stream));     // passes in flight still read the old scene
+    c->haveScene = false;
+    auto grow = [&](auto** ptr, size_t& cap, size_t need) -> cudaError_t {
+        using T = typename std::remove_pointer<typename std::remove_pointer<decltype(ptr)>::type>::type;
+        if (need <= cap && *ptr) return cudaSuccess;
+        cudaFree(*ptr); *ptr = nullptr; cap = 0;
+        const size_t n = std::max<size_t>(need + need / 8, 1);
+        cudaError_t e = cudaMalloc(reinterpret_cast<void**>(ptr), n * sizeof(T));
+        if (e == cudaSuccess) cap = n;
         return e;
     };
-    RT_CUDA(c, upload(&c->dNodes, nodes));
-    RT_CUDA(c, upload(&c->dTris, triRecs));
-    RT_CUDA(c, upload(&c->dShade, shadeRecs));
-    RT_CUDA(c, upload(&c->dTriId, triIds));
-    RT_CUDA(c, upload(&c->dBig, bigLeaves));
-    RT_CUDA(c, cudaStreamSynchronize(c->stream));   // the host vectors die at return
+    const size_t nSlotsAll = triIds.size();
+    RT_CUDA(c, grow(&c->dNodes, c->capNodes, nodes.size()));
+    RT_CUDA(c, grow(&c->dTriId, c->capSlots, nSlotsAll));
+    if (!c->dTris || !c->dShade || c->capSlots != c->capSlotRecs) {
+        cudaFree(c->dTris); cudaFree(c->dShade); c->dTris = nullptr; c->dShade = nullptr; c->capSlotRecs = 0;
+        RT_CUDA(c, cudaMalloc(reinterpret_cast<void**>(&c->dTris), c->capSlots * sizeof(TriRec)));
+        RT_CUDA(c, cudaMalloc(reinterpret_cast<void**>(&c->dShade), c->capSlots * sizeof(ShadeRec)));
+        c->capSlotRecs = c->capSlots;
+    }
+    RT_CUDA(c, grow(&c->dBig, c->capBig, bigLeaves.size()));
+    RT_CUDA(c, grow(&c->dRawTris, c->capRaw, size_t(nTris) * (sizeof(HostTri) / sizeof(float4))));
+    const size_t bytesNodes = nodes.size() * sizeof(NodeRec), bytesIds = nSlotsAll * sizeof(uint32_t),
+                 bytesBig = bigLeaves.size() * sizeof(uint2);
+    const size_t offIds = bytesNodes, offBig = (offIds + bytesIds + 15) & ~size_t(15), stageBytes = offBig + bytesBig;
+    if (stageBytes > c->hStageBytes) {
+        cudaFreeHost(c->hStage); c->hStage = nullptr; c->hStageBytes = 0;
+        RT_CUDA(c, cudaMallocHost(&c->hStage, stageBytes + stageBytes / 8));
+        c->hStageBytes = stageBytes + stageBytes / 8;
+    }
+    char* stage = static_cast<char*>(c->hStage);
+    if (bytesNodes) std::memcpy(stage, nodes.data(), bytesNodes);
+    if (bytesIds) std::memcpy(stage + offIds, triIds.data(), bytesIds);
+    if (bytesBig) std::memcpy(stage + offBig, bigLeaves.data(), bytesBig);
+    if (nTris) RT_CUDA(c, cudaMemcpyAsync(c->dRawTris, tris, size_t(nTris) * sizeof(HostTri), cudaMemcpyHostToDevice, c->stream));
+    if (bytesNodes) RT_CUDA(c, cudaMemcpyAsync(c->dNodes, stage, bytesNodes, cudaMemcpyHostToDevice, c->stream));
+    if (bytesIds) RT_CUDA(c, cudaMemcpyAsync(c->dTriId, stage + offIds, bytesIds, cudaMemcpyHostToDevice, c->stream));
+    if (bytesBig) RT_CUDA(c, cudaMemcpyAsync(c->dBig, stage + offBig, bytesBig, cudaMemcpyHostToDevice, c->stream));
+    if (nSlotsAll)
+        RT_CUDA(c, rtLaunchBuildRecords(c->dRawTris, c->dTriId, uint32_t(nSlotsAll), c->dTris, c->dShade, c->stream));
+    RT_CUDA(c, cudaStreamSynchronize(c->stream));     // glBufferData semantics: the caller's arrays are free at return
     sc.nodes = c->dNodes; sc.tris = c->dTris; sc.shade = c->dShade; sc.triId = c->dTriId; sc.bigLeaves = c->dBig;
     sc.nNodes = uint32_t(nodes.size());
-    sc.nSlots = uint32_t(triRecs.size());
+    sc.nSlots = uint32_t(nSlotsAll);
     c->scene = sc;
     c->haveScene = true;
     return RT_OK;

@@ -171,6 +171,34 @@ __global__ void rtFinishSumKernel(float4* __restrict__ target, size_t n, float f
     }
 }
 
+// rt_scene_upload: one thread per triangle slot builds its TriRec (v0, the two edges and their cross product, exactly
+// the operations of fragment.glsl:112-116 in that order) and ShadeRec from the caller's 144-byte triangle (nine
+// float4: v0p v0n v1p v1n v2p v2n color emc surface; scene.py:13-30).
+__global__ void rtBuildRecordsKernel(const float4* __restrict__ raw, const uint32_t* __restrict__ triId, uint32_t nSlots,
+                                     TriRec* __restrict__ tris, ShadeRec* __restrict__ shade) {
+    const uint32_t step = gridDim.x * blockDim.x;
+    for (uint32_t slot = blockIdx.x * blockDim.x + threadIdx.x; slot < nSlots; slot += step) {
+        const float4* q = raw + size_t(triId[slot]) * 9;
+        const float4 v0 = __ldg(q), n0 = __ldg(q + 1), v1 = __ldg(q + 2), n1 = __ldg(q + 3), v2 = __ldg(q + 4),
+                     n2 = __ldg(q + 5), col = __ldg(q + 6), emc = __ldg(q + 7), surf = __ldg(q + 8);
+        const float abx = __fsub_rn(v1.x, v0.x), aby = __fsub_rn(v1.y, v0.y), abz = __fsub_rn(v1.z, v0.z);
+        const float acx = __fsub_rn(v2.x, v0.x), acy = __fsub_rn(v2.y, v0.y), acz = __fsub_rn(v2.z, v0.z);
+        const float nx = __fsub_rn(__fmul_rn(aby, acz), __fmul_rn(acy, abz));
+        const float ny = __fsub_rn(__fmul_rn(abz, acx), __fmul_rn(acz, abx));
+        const float nz = __fsub_rn(__fmul_rn(abx, acy), __fmul_rn(acx, aby));
+        float4* t = reinterpret_cast<float4*>(tris + slot);
+        t[0] = make_float4(v0.x, v0.y, v0.z, abx);
+        t[1] = make_float4(aby, abz, acx, acy);
+        t[2] = make_float4(acz, nx, ny, nz);
+        float4* s = reinterpret_cast<float4*>(shade + slot);
+        s[0] = make_float4(n0.x, n0.y, n0.z, n1.x);
+        s[1] = make_float4(n1.y, n1.z, n2.x, n2.y);
+        s[2] = make_float4(n2.z, col.x, col.y, col.z);
+        s[3] = make_float4(emc.x, emc.y, emc.z, surf.x);
+        s[4] = make_float4(surf.y, 0.0f, 0.0f, 0.0f);
+    }
+}
+
 }  // namespace
 
 // ------------------------------------------------------------------------------------- launchers
@@ -391,5 +419,12 @@ cudaError_t rtLaunchBandCopy(float4* target, float4* dense, int width, int rows,
 
 cudaError_t rtLaunchFinishSum(float4* target, size_t n, float frames, cudaStream_t stream) {
     rtFinishSumKernel<<<148 * 8, 256, 0, stream>>>(target, n, frames);
+    return cudaGetLastError();
+}
+
+cudaError_t rtLaunchBuildRecords(const float4* raw, const uint32_t* triId, uint32_t nSlots, TriRec* tris, ShadeRec* shade,
+                                 cudaStream_t stream) {
+    const unsigned blocks = std::min<unsigned>(148 * 8, (nSlots + 255) / 256);
+    rtBuildRecordsKernel<<<blocks, 256, 0, stream>>>(raw, triId, nSlots, tris, shade);
     return cudaGetLastError();
 }
