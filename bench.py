@@ -322,7 +322,8 @@ def run_gpu(args):
         res = {"cfg": cfg, "counters": total, "ms_per_step": ms_step, "kernel_ms": kernel_ms,
                "mrays_s": total["rays_traced"] / (ms_step * 1e-3) / 1e6,
                "ref_equiv_mrays_s": total["rays"] / (ms_step * 1e-3) / 1e6, "clocks": clocks,
-               "local_alg_bytes": local_alg_bytes, "launches": steps, "phases_ms": phases}   # traversal-kernel passes; the caller multiplies by kernels per pass
+               "local_alg_bytes": local_alg_bytes, "launches": steps, "phases_ms": phases,
+               "pass_launches": ctx.last_pass_launches()}   # traversal-kernel passes; the caller multiplies by kernels per pass
         if with_e2e:
             # end to end through the C ABI with HOST buffers: scene upload (H2D), uniforms, draw, gather, and the
             # RGBA32F read-back (D2H) on rank 0, every step
@@ -400,9 +401,9 @@ def run_gpu(args):
             "reference_equivalent": {"rays_per_step": cnt["rays"], "mrays_s": main["ref_equiv_mrays_s"]},
             "e2e": main["e2e"], "roofline": roofline, "clocks": main["clocks"], "phases_ms": main["phases_ms"],
             # this repo's kernels launched by rank 0 inside the timed region: the pass (1 kernel; the samples variant
-            # launches its primary stage + 6 rounds of evaluation/chain kernels) + band gather (1) and scatters (N - 1)
-            "gpu_launches": main["launches"] * ((13 if variant == "samples" else 2 if variant == "wavefront" else 1)
-                                                + (world if world > 1 else 0))}
+            # launches its primary stage + rounds of sort/evaluate/chain kernels: the library reports the count) + band
+            # gather (1) and scatters (N - 1)
+            "gpu_launches": main["launches"] * (main["pass_launches"] + (world if world > 1 else 0))}
 
     if world == 1 and not args.no_cpu:
         line["cpu_baseline"] = cpu_baseline(args)

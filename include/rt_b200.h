@@ -110,6 +110,8 @@ int rt_scene_free(rt_ctx* ctx);
 
 int rt_set_params(rt_ctx* ctx, const rt_params* params);
 int rt_set_variant(rt_ctx* ctx, int variant);
+/* Kernels the last rt_render_pass launched (1 for the single-kernel variants; AUTO may pick a multi-stage one). */
+int rt_last_pass_launches(rt_ctx* ctx);
 
 /* Two width x height RGBA32F accumulation targets, cleared to 0; accum_index = 0, like screen.py:61-66. */
 int rt_target_create(rt_ctx* ctx, int width, int height);

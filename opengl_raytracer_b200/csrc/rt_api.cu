@@ -26,6 +26,8 @@ cudaError_t rtLaunchPool(const PassParams& P, bool count, bool ids, int sms, cud
 cudaError_t rtLaunchWavefront(const PassParams& P, bool count, bool ids, int sms, cudaStream_t stream);
 cudaError_t rtLaunchSamples(const PassParams& P, bool ids, int sms, uint32_t* todoA, uint32_t* todoB, cudaStream_t stream);
 int rtSpecRounds();
+int rtSpecLaunches();
+int rtSpecWorkUints();
 cudaError_t rtSpecInit();
 int rtSpecTableK(int raysPerPixel, int nBounces);
 cudaError_t rtLaunchToRgba8(const float4* src, uchar4* dst, size_t n, cudaStream_t stream);
@@ -80,6 +82,8 @@ struct rt_ctx {
     size_t specRecords = 0, specBufEntries = 0;
     unsigned int* dWorkArr = nullptr;     // work counters of the rounds + todo counts
     uint32_t* dTodo[2] = {nullptr, nullptr};
+    uint32_t* dChainClass = nullptr;
+    int lastLaunches = 0;                 // kernel launches of the last pass (rt_last_pass_launches)
     uint32_t* dChainK = nullptr;
     float4* dChainColor = nullptr;
 };
@@ -139,8 +143,8 @@ void freeScene(rt_ctx* c) {
 void freeQueue(rt_ctx* c) {
     cudaFree(c->dQueueA); cudaFree(c->dQueueB); cudaFree(c->dQueuePix); cudaFree(c->dQueueWork);
     cudaFree(c->dQueueC); cudaFree(c->dQueueD); cudaFree(c->dQueueE); cudaFree(c->dSpecBuf);
-    cudaFree(c->dTodo[0]); cudaFree(c->dTodo[1]); cudaFree(c->dChainK); cudaFree(c->dChainColor);
-    c->dTodo[0] = c->dTodo[1] = nullptr; c->dChainK = nullptr; c->dChainColor = nullptr;
+    cudaFree(c->dTodo[0]); cudaFree(c->dTodo[1]); cudaFree(c->dChainK); cudaFree(c->dChainColor); cudaFree(c->dChainClass);
+    c->dTodo[0] = c->dTodo[1] = nullptr; c->dChainK = nullptr; c->dChainColor = nullptr; c->dChainClass = nullptr;
     c->dQueueA = c->dQueueB = nullptr; c->dQueuePix = nullptr; c->dQueueWork = nullptr;
     c->dQueueC = c->dQueueD = c->dQueueE = c->dSpecBuf = nullptr;
     c->queueCapacity = 0; c->specRecords = 0; c->specBufEntries = 0;
@@ -155,12 +159,13 @@ cudaError_t ensureSpec(rt_ctx* c, size_t ownedPixels, int K, uint32_t* capacityO
     if (e != cudaSuccess) return e;
     if (c->specRecords < c->queueCapacity) {
         cudaFree(c->dQueueC); cudaFree(c->dQueueD); cudaFree(c->dQueueE);
-        cudaFree(c->dTodo[0]); cudaFree(c->dTodo[1]); cudaFree(c->dChainK); cudaFree(c->dChainColor);
+        cudaFree(c->dTodo[0]); cudaFree(c->dTodo[1]); cudaFree(c->dChainK); cudaFree(c->dChainColor); cudaFree(c->dChainClass);
         c->dQueueC = c->dQueueD = c->dQueueE = nullptr; c->specRecords = 0;
-        c->dTodo[0] = c->dTodo[1] = nullptr; c->dChainK = nullptr; c->dChainColor = nullptr;
+        c->dTodo[0] = c->dTodo[1] = nullptr; c->dChainK = nullptr; c->dChainColor = nullptr; c->dChainClass = nullptr;
         if ((e = cudaMalloc(&c->dTodo[0], c->queueCapacity * sizeof(uint32_t))) != cudaSuccess) return e;
         if ((e = cudaMalloc(&c->dTodo[1], c->queueCapacity * sizeof(uint32_t))) != cudaSuccess) return e;
         if ((e = cudaMalloc(&c->dChainK, c->queueCapacity * sizeof(uint32_t))) != cudaSuccess) return e;
+        if ((e = cudaMalloc(&c->dChainClass, c->queueCapacity * sizeof(uint32_t))) != cudaSuccess) return e;
         if ((e = cudaMalloc(&c->dChainColor, c->queueCapacity * sizeof(float4))) != cudaSuccess) return e;
         if ((e = cudaMalloc(&c->dQueueC, c->queueCapacity * sizeof(float4))) != cudaSuccess) return e;
         if ((e = cudaMalloc(&c->dQueueD, c->queueCapacity * sizeof(float4))) != cudaSuccess) return e;
@@ -244,7 +249,7 @@ int rt_create(rt_ctx** out, int device) {
         cudaMalloc(&c->dCounters, RT_CNT_COUNT * sizeof(unsigned long long)) != cudaSuccess ||
         cudaMalloc(&c->dWork, sizeof(unsigned int)) != cudaSuccess ||
         cudaMalloc(&c->dQueueCount, sizeof(unsigned int)) != cudaSuccess ||
-        cudaMalloc(&c->dWorkArr, 64 * sizeof(unsigned int)) != cudaSuccess || rtSpecInit() != cudaSuccess) {
+        cudaMalloc(&c->dWorkArr, size_t(rtSpecWorkUints()) * sizeof(unsigned int)) != cudaSuccess || rtSpecInit() != cudaSuccess) {
         delete c;
         return RT_ERR_CUDA;
     }
@@ -575,7 +580,8 @@ int renderPass(rt_ctx* c, int frameNumber, int tileX, int tileY, int flags, int 
         P.queueA = c->dQueueA; P.queueB = c->dQueueB; P.queueC = c->dQueueC; P.queueD = c->dQueueD; P.queueE = c->dQueueE;
         P.queueCount = c->dQueueCount; P.specBuf = c->dSpecBuf; P.specK = K; P.specCapacity = capacity;
         P.specBufEntries = uint32_t(std::min<size_t>(c->specBufEntries, 0xffffffffu));
-        P.workCounters = c->dWorkArr; P.todoCount = c->dWorkArr + 32; P.chainK = c->dChainK; P.chainColor = c->dChainColor;
+        P.workCounters = c->dWorkArr; P.todoCount = c->dWorkArr + 32; P.classCount = c->dWorkArr + 64;
+        P.chainK = c->dChainK; P.chainColor = c->dChainColor; P.chainClass = c->dChainClass;
         e = rtLaunchSamples(P, P.primaryIds != nullptr, c->smCount, c->dTodo[0], c->dTodo[1], c->stream);
     } else if (variant == RT_VARIANT_WAVEFRONT) {
         e = ensureQueue(c, P.counters != nullptr);
@@ -590,6 +596,7 @@ int renderPass(rt_ctx* c, int frameNumber, int tileX, int tileY, int flags, int 
     else
         e = rtLaunchPixel(P, P.counters != nullptr, P.primaryIds != nullptr, c->stream);
     if (e != cudaSuccess) return fail(c, RT_ERR_CUDA, "kernel launch: %s", cudaGetErrorString(e));
+    c->lastLaunches = variant == RT_VARIANT_SAMPLES ? rtSpecLaunches() : variant == RT_VARIANT_WAVEFRONT ? 2 : 1;
     c->accumIndex = next;
     return RT_OK;
 }
@@ -658,6 +665,8 @@ int rt_read_accum_f32(rt_ctx* c, float* dst) {
 
 // Upload an accumulation image into the current target (checkpoint restore; the GL counterpart would be
 // glTexSubImage2D on accum_tex[accum_index], which the reference never does).
+int rt_last_pass_launches(rt_ctx* c) { return c ? c->lastLaunches : 0; }
+
 int rt_write_accum_f32(rt_ctx* c, const float* src) {
     if (!c || !src) return RT_ERR_INVALID;
     if (!c->target[0]) return fail(c, RT_ERR_STATE, "no target");

@@ -347,8 +347,18 @@ cudaError_t rtLaunchWavefront(const PassParams& P, bool count, bool ids, int sms
 }
 
 // ---- SAMPLES variant: primary stage -> queue -> rounds of [parallel evaluation of F(k) -> chain]
-int rtSpecTableK(int raysPerPixel, int nBounces) { (void)nBounces; return spec::tableK(raysPerPixel); }
+int rtSpecTableK(int raysPerPixel, int nBounces) {
+    (void)nBounces;
+    if (const char* e = getenv("RT_SPEC_K0")) {           // experiments: round 0's table size as a percentage of rays_per_pixel
+        const int pct = atoi(e);
+        if (pct >= 100) return std::min(spec::kMaxK / 4, std::max(8, int((long long)raysPerPixel * pct / 100)));
+    }
+    return spec::tableK(raysPerPixel);
+}
 int rtSpecRounds() { return spec::kRounds; }
+// layout of the samples variant's counter array: [0,32) work counters (2 per round), [32,64) parked pixels per round,
+// [64, 64 + (rounds + 1) * 32) size-class counts per round
+constexpr int kSpecWorkUints = 64 + (spec::kRounds + 1) * spec::kClassStride;
 
 cudaError_t rtSpecInit() {
     static uint2 lo[spec::kJumpLo], hi[spec::kJumpHi];
@@ -358,13 +368,17 @@ cudaError_t rtSpecInit() {
     return cudaMemcpyToSymbol(spec::cJumpHi, hi, sizeof hi);
 }
 
+// kernel launches of one samples pass that uses tables: stage 1 + round 0 (evaluate, chain) + 3 per later round
+int rtSpecLaunches() { return 3 + 3 * (spec::kRounds - 1); }
+int rtSpecWorkUints() { return kSpecWorkUints; }
+
 cudaError_t rtLaunchSamples(const PassParams& Pin, bool ids, int sms, uint32_t* todoA, uint32_t* todoB, cudaStream_t stream) {
     PassParams P = Pin;
     if (P.ownedW <= 0 || P.ownedH <= 0) return cudaSuccess;
     if (const char* e = getenv("RT_VOTE_TUNE")) sscanf(e, "%d,%d,%d", &P.tune[0], &P.tune[1], &P.tune[2]);
-    cudaError_t e = cudaMemsetAsync(P.workCounters, 0, 2 * spec::kRounds * sizeof(unsigned int), stream);
+    // workCounters, todoCount and classCount are one array (rt_api.cu): cleared with one memset
+    cudaError_t e = cudaMemsetAsync(P.workCounters, 0, size_t(kSpecWorkUints) * sizeof(unsigned int), stream);
     if (e != cudaSuccess) return e;
-    if ((e = cudaMemsetAsync(P.todoCount, 0, (spec::kRounds + 1) * sizeof(unsigned int), stream)) != cudaSuccess) return e;
     if ((e = cudaMemsetAsync(P.queueCount, 0, sizeof(unsigned int), stream)) != cudaSuccess) return e;
     const size_t smem = spec::smemBytes(P.scene.stackDepth);
     const size_t smemEval = vote::smemBytes(P.scene.stackDepth);
@@ -389,18 +403,18 @@ cudaError_t rtLaunchSamples(const PassParams& Pin, bool ids, int sms, uint32_t* 
     const int gridEval = int(std::min<long long>((long long)sms * std::max(perSmEval, 1), std::max<long long>(wantEval, 1)));
     const int gridChain = int(std::min<long long>((long long)sms * std::max(perSmChain, 1), std::max<long long>(wantChain, 1)));
     // the rounds are launched unconditionally: a round without pixels (or the whole speculation, when stage 1 found
-    // that most primary rays hit) is a kernel that reads one counter and returns
-    const int K0 = P.specK;
+    // that most primary rays hit) is three kernels that read a counter and return
+    P.todoFlat = todoA;
+    P.todoSorted = todoB;
+    const int gridSort = sms * 2;
     for (int round = 0; round < spec::kRounds; round++) {
         P.specRound = round;
-        // round 0: rays_per_pixel * 1.25 offsets; then top-ups that double (a chain can run to rays_per_pixel * nBounces)
-        P.specK = round == 0 ? K0 : std::min(spec::kMaxK / 4, spec::laterK(P.raysPerPixel) << (round - 1));
-        P.todoIn = (round & 1) ? todoA : todoB;
-        P.todoOut = (round & 1) ? todoB : todoA;
-        if (P.specK > 0 && P.specCapacity > 0) spec::rtSpecEvalKernel<<<gridEval, spec::kThreads, smemEval, stream>>>(P);
+        const bool tables = P.specK > 0 && P.specCapacity > 0;
+        if (round > 0) spec::rtSpecSortKernel<<<gridSort, spec::kThreads, 0, stream>>>(P);
+        if (tables) spec::rtSpecEvalKernel<<<gridEval, spec::kThreads, smemEval, stream>>>(P);
         spec::rtSpecChainKernel<<<gridChain, spec::kThreads, smem, stream>>>(P);
         if ((e = cudaGetLastError()) != cudaSuccess) return e;
-        if (P.specK <= 0 || P.specCapacity == 0) break;
+        if (!tables) break;
     }
     return cudaSuccess;
 }

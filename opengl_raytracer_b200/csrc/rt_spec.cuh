@@ -32,7 +32,7 @@
 namespace spec {
 
 constexpr int kThreads = 128;
-constexpr int kRounds = 6;                   // speculative rounds before a pixel's remaining samples run one by one
+constexpr int kRounds = 4;                   // speculative rounds: 0 = every queued pixel, 1.. = the chains that ran further
 constexpr int kJumpLo = 256, kJumpHi = 64;   // offsets k < kJumpLo * kJumpHi can be jumped to
 constexpr int kMaxK = kJumpLo * kJumpHi;
 __constant__ uint2 cJumpLo[kJumpLo];         // (a, c) of 3k draws, k < 256: state' = a * state + c
@@ -42,9 +42,16 @@ RT_DEV uint32_t jumpSeed(uint32_t seed, unsigned int k) {
     return (seed * lo.x + lo.y) * hi.x + hi.y;
 }
 
-// Table sizes: round 0 covers rays_per_pixel samples at up to 1.25 hits each (open-sky chains run at 1.0-1.3); the
-// later rounds are top-ups that double, for the pixels whose chain runs further (at most nBounces hits per sample).
-// Measured alternative (round sizes derived on the device from the parked chains' own rates): slower, 34.0 vs 31.9 ms.
+// Table sizes.  Round 0 gives every queued pixel rays_per_pixel samples at up to 1.25 hits each (open-sky chains run
+// at 1.0-1.3).  A chain that leaves its table knows its own rate (hits so far / samples so far), so the pixel asks for
+// what its remaining samples should need, with a margin, rounded up to a size class (8, 12, 16, 24, 32, 48, ...); the
+// last round asks for the bound (remaining samples x nBounces hits), which always suffices.  A round is then ONE
+// evaluation launch over all classes, and a 64-spp frame is done in three rounds where fixed doubling top-ups took
+// six (each of which costs at least one path latency, 0.3 ms, however few pixels are left).
+constexpr int kClasses = 22;
+constexpr int kClassStride = 32;             // uints per round in PassParams::classCount: [c] pixels of class c, [30] entries reserved
+constexpr int kReserved = 30;
+__host__ __device__ inline unsigned int classK(int c) { return ((c & 1) ? 12u : 8u) << (c >> 1); }
 inline int laterK(int raysPerPixel) { return raysPerPixel / 4 > 8 ? (raysPerPixel / 4 < 256 ? raysPerPixel / 4 : 256) : 8; }
 inline int tableK(int raysPerPixel) {
     const int k = raysPerPixel + laterK(raysPerPixel);
@@ -84,11 +91,31 @@ RT_DEV bool specMode(const PassParams& P, unsigned int queued) {
     return 2ull * queued <= (unsigned long long)P.ownedW * (unsigned long long)P.ownedH && queued <= P.specCapacity;
 }
 
-// Table entries per pixel in this round: the launch's size, clamped so the round's pixels fit the buffer (later
-// rounds have few pixels and long tables).
+// Round 0's table entries per pixel: the launch's size, clamped so that the queued pixels fit the buffer.
 RT_DEV unsigned int roundK(const PassParams& P, unsigned int pixelsThisRound) {
     const unsigned int fit = P.specBufEntries / (pixelsThisRound > 0u ? pixelsThisRound : 1u);
     return min((unsigned int)P.specK, fit);
+}
+
+// Where a round's pixels and table entries are: class c holds pixels [pixBase[c], pixBase[c+1]) of the round's sorted
+// list, each with K[c] entries starting at itemBase[c] (an item's index is its entry in the table).  Round 0 is one
+// class holding every queued pixel.
+struct ClassTable {
+    unsigned int itemBase[kClasses + 1], pixBase[kClasses + 1], K[kClasses];
+};
+RT_DEV void buildClassTable(const PassParams& P, int round, unsigned int queued, bool speculative, ClassTable& T) {
+    if (threadIdx.x == 0) {
+        unsigned int items = 0, pix = 0;
+        for (int c = 0; c < kClasses; c++) {
+            unsigned int n, K;
+            if (round == 0) { n = c == 0 ? queued : 0u; K = speculative ? roundK(P, queued) : 0u; }
+            else { n = P.classCount[round * kClassStride + c]; K = classK(c); }
+            T.itemBase[c] = items; T.pixBase[c] = pix; T.K[c] = K;
+            items += n * K; pix += n;
+        }
+        T.itemBase[kClasses] = items; T.pixBase[kClasses] = pix;
+    }
+    __syncthreads();
 }
 
 // ------------------------------------------------------------------------------------------ stage 1
@@ -204,12 +231,12 @@ __global__ void __launch_bounds__(kThreads) rtSpecEvalKernel(const __grid_consta
     const unsigned int queued = *P.queueCount;
     if (!specMode(P, queued)) return;
     const int round = P.specRound;
-    const unsigned int pixelsThisRound = round == 0 ? queued : P.todoCount[round];
+    __shared__ ClassTable T;
+    buildClassTable(P, round, queued, true, T);
     const uint32_t lane = threadIdx.x & 31u;
     uint2* const stack = smem + threadIdx.x;
     const uint32_t stride = kThreads;
-    const unsigned int K = roundK(P, pixelsThisRound);
-    const unsigned int totalItems = pixelsThisRound * K;
+    const unsigned int totalItems = T.itemBase[kClasses];
     unsigned int* const workCounter = P.workCounters + 2 * round;
     const f3 zero = mk3(0.f, 0.f, 0.f);
     const f3 sky = scale3(mk3(0.1f, 0.6f, 0.92f), P.skyBrightness);
@@ -275,8 +302,11 @@ __global__ void __launch_bounds__(kThreads) rtSpecEvalKernel(const __grid_consta
                         L.mode = MODE_DONE; L.needPixel = false;
                     } else {
                         // item -> (t-th pixel of this round, kk-th offset past the pixel's chain position)
-                        const unsigned int t = item / K, kk = item - t * K;
-                        const unsigned int j = round == 0 ? t : P.todoIn[t];
+                        int c = 0;
+                        while (item >= T.itemBase[c + 1]) c++;
+                        const unsigned int K = T.K[c], rel = item - T.itemBase[c], tIn = rel / K, kk = rel - tIn * K;
+                        const unsigned int t = T.pixBase[c] + tIn;
+                        const unsigned int j = round == 0 ? t : P.todoSorted[t];
                         const unsigned int k = (round == 0 ? 0u : P.chainK[j]) + kk;
                         const Record r = loadRecord(P, j);
                         L.seed = jumpSeed(r.seed, k);           // RNG state after 3k draws
@@ -305,8 +335,9 @@ __global__ void __launch_bounds__(kThreads) rtSpecEvalKernel(const __grid_consta
 
 // ------------------------------------------------------------------------------------------ stage 3
 // One thread per pixel of the round: trace() (fragment.glsl:352-366) as a chain through the table of F.  A chain
-// that leaves its table parks (k, sample, colour) and joins the next round, whose table starts at its k; after the
-// last round — or when there is no table at all — the remaining samples are evaluated one after the other.
+// that leaves its table parks (k, sample, colour), reserves a table of the size class its own rate predicts and joins
+// the next round; after the last round — or when there is no table at all, or no room for one — the remaining samples
+// are evaluated one after the other.
 __global__ void __launch_bounds__(kThreads) rtSpecChainKernel(const __grid_constant__ PassParams P) {
     extern __shared__ uint2 stackMem[];
     const uint32_t lane = threadIdx.x & 31u;
@@ -316,11 +347,13 @@ __global__ void __launch_bounds__(kThreads) rtSpecChainKernel(const __grid_const
     const int round = P.specRound;
     const bool speculative = specMode(P, queued);
     if (round > 0 && !speculative) return;
-    const unsigned int pixelsThisRound = round == 0 ? queued : P.todoCount[round];
-    const unsigned int K = speculative ? roundK(P, pixelsThisRound) : 0u;   // 0: every sample on demand
+    __shared__ ClassTable T;
+    buildClassTable(P, round, queued, speculative, T);
+    const unsigned int pixelsThisRound = T.pixBase[kClasses];
     const f3 sky = scale3(mk3(0.1f, 0.6f, 0.92f), P.skyBrightness);
     const bool lambertian = P.lambertian != 0;
     unsigned int* const workCounter = P.workCounters + 2 * round + 1;
+    unsigned int* const nextClass = P.classCount + (round + 1) * kClassStride;
     for (;;) {
         unsigned int base = 0;
         if (lane == 0) base = atomicAdd(workCounter, 32u);
@@ -330,7 +363,10 @@ __global__ void __launch_bounds__(kThreads) rtSpecChainKernel(const __grid_const
         bool again = false;
         unsigned int j = 0;
         if (t < pixelsThisRound) {
-            j = round == 0 ? t : P.todoIn[t];
+            int c = 0;
+            while (t >= T.pixBase[c + 1]) c++;
+            const unsigned int K = T.K[c];                     // 0: every sample on demand
+            j = round == 0 ? t : P.todoSorted[t];
             const Record r = loadRecord(P, j);
             f3 color = mk3(0.f, 0.f, 0.f);
             unsigned int k = 0;
@@ -342,17 +378,39 @@ __global__ void __launch_bounds__(kThreads) rtSpecChainKernel(const __grid_const
                 k = P.chainK[j];
             }
             const unsigned int k0 = k;
-            const float4* table = P.specBuf + size_t(t) * K;
+            const float4* table = P.specBuf + size_t(T.itemBase[c]) + size_t(t - T.pixBase[c]) * K;
             for (; s < P.raysPerPixel && k - k0 < K; s++) {
                 const float4 f = table[k - k0];
                 color = add3(color, mk3(f.x, f.y, f.z));      // trace(), :359
                 k += (unsigned int)__float_as_int(f.w);
             }
-            if (s < P.raysPerPixel && K > 0 && round + 1 < kRounds && k + K + 8u < (unsigned int)kMaxK) {
-                P.chainColor[j] = make_float4(color.x, color.y, color.z, __int_as_float(s));
-                P.chainK[j] = k;
-                again = true;
-            } else {
+            if (s < P.raysPerPixel && K > 0 && round + 1 < kRounds) {
+                // the table this chain asks for: its rate so far x the samples left, with a margin (a sample's hit count
+                // varies by a few) — or the bound, in the last round and where there is no rate yet
+                const unsigned long long rem = (unsigned long long)(P.raysPerPixel - s);
+                const unsigned long long bound = rem * (unsigned long long)max(P.nBounces, 1);
+                unsigned long long need = bound;
+                if (round + 2 < kRounds && s > 0) {
+                    const float predicted = float(k) / float(s) * float(rem) * 1.125f + 2.0f * sqrtf(float(rem)) + 2.0f;
+                    need = min(bound, (unsigned long long)predicted);
+                }
+                int cls = 0;
+                while (cls < kClasses && (unsigned long long)classK(cls) < need) cls++;
+                if (cls < kClasses && (unsigned long long)k + classK(cls) + 8ull < (unsigned long long)kMaxK) {
+                    const unsigned int Kc = classK(cls);
+                    const unsigned int before = atomicAdd(nextClass + kReserved, Kc);
+                    if ((unsigned long long)before + Kc <= (unsigned long long)P.specBufEntries) {
+                        const unsigned int rank = atomicAdd(nextClass + cls, 1u);
+                        P.chainColor[j] = make_float4(color.x, color.y, color.z, __int_as_float(s));
+                        P.chainK[j] = k;
+                        P.chainClass[j] = (rank << 5) | (unsigned int)cls;
+                        again = true;
+                    } else {
+                        atomicSub(nextClass + kReserved, Kc);   // the buffer is full: this pixel finishes below
+                    }
+                }
+            }
+            if (!again) {
                 if (s < P.raysPerPixel) {
                     uint32_t seed = jumpSeed(r.seed, k);
                     for (; s < P.raysPerPixel; s++) color = add3(color, evalPath(P, r, seed, st, sky, lambertian));
@@ -368,8 +426,27 @@ __global__ void __launch_bounds__(kThreads) rtSpecChainKernel(const __grid_const
             const int leader = __ffs(m) - 1;
             if (int(lane) == leader) at = atomicAdd(P.todoCount + round + 1, (unsigned int)__popc(m));
             at = __shfl_sync(0xffffffffu, at, leader);
-            if (again) P.todoOut[at + (unsigned int)__popc(m & ((1u << lane) - 1u))] = j;
+            if (again) P.todoFlat[at + (unsigned int)__popc(m & ((1u << lane) - 1u))] = j;
         }
+    }
+}
+
+// Between two rounds: the parked pixels, listed in the order they parked, are put in class order (a pixel's place is
+// its class's first place + the rank it drew when it parked), which is the order the round's table is laid out in.
+__global__ void __launch_bounds__(kThreads) rtSpecSortKernel(const __grid_constant__ PassParams P) {
+    const unsigned int queued = *P.queueCount;
+    if (!specMode(P, queued)) return;
+    const int round = P.specRound;
+    __shared__ unsigned int pixBase[kClasses];
+    if (threadIdx.x == 0) {
+        unsigned int pix = 0;
+        for (int c = 0; c < kClasses; c++) { pixBase[c] = pix; pix += P.classCount[round * kClassStride + c]; }
+    }
+    __syncthreads();
+    const unsigned int n = P.todoCount[round];
+    for (unsigned int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        const unsigned int j = P.todoFlat[i], cr = P.chainClass[j];
+        P.todoSorted[pixBase[cr & 31u] + (cr >> 5)] = j;
     }
 }
 

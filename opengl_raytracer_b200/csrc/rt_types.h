@@ -96,8 +96,10 @@ struct PassParams {
     uint32_t specBufEntries;        // float4 entries of specBuf
     unsigned int* workCounters;     // 2 per round (evaluation, chain), zeroed per pass
     unsigned int* todoCount;        // [rounds + 1] pixels whose chain left its table
-    const uint32_t* todoIn;         // this round's pixels (round > 0)
-    uint32_t* todoOut;              // next round's pixels
+    uint32_t* todoFlat;             // pixels parked for the next round, in parking order
+    uint32_t* todoSorted;           // this round's pixels in class order (round > 0)
+    unsigned int* classCount;       // [rounds + 1][32]: pixels per size class, [30] = table entries reserved
+    uint32_t* chainClass;           // per queued pixel: (rank within its class << 5) | class
     uint32_t* chainK;               // parked chain position per queued pixel
     float4* chainColor;             // parked colour sum (xyz) and sample index (w)
     int32_t specRound;

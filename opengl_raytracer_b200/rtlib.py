@@ -81,6 +81,7 @@ def load_library(path: str | None = None):
         "rt_scene_free": (i, [vp]),
         "rt_set_params": (i, [vp, P(RtParams)]),
         "rt_set_variant": (i, [vp, i]),
+        "rt_last_pass_launches": (i, [vp]),
         "rt_target_create": (i, [vp, i, i]),
         "rt_target_clear": (i, [vp]),
         "rt_target_free": (i, [vp]),
@@ -191,6 +192,9 @@ class Context:
 
     def set_variant(self, variant):
         self._check(self.lib.rt_set_variant(self.handle, VARIANTS.get(variant, variant)))
+
+    def last_pass_launches(self) -> int:
+        return int(self.lib.rt_last_pass_launches(self.handle))
 
     def set_stream(self, cuda_stream: int | None):
         self._check(self.lib.rt_set_stream(self.handle, ctypes.c_void_p(cuda_stream or 0)))

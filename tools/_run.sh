@@ -1,5 +1,2 @@
-PYTEST_K="samples" VARIANTS=samples bash tools/gpu_quick.sh
-for B in 1 8; do
-python tools/prof_case.py cfg4_open 3840 2160 64 samples 2 $B > /dev/null 2>&1 && ncu --metrics gpu__time_duration.sum --clock-control none --csv --log-file gpurun_out/spec_launches_$B.csv python tools/prof_case.py cfg4_open 3840 2160 64 samples 2 $B > /dev/null 2>&1
-grep -v "^==" gpurun_out/spec_launches_$B.csv | awk -F'","' 'NR>1{print $5, $NF}' | tail -3
-done
+python -m pytest tests -q -x -m gpu 2>&1 | tail -3
+python bench.py --no-box --no-cpu --variant samples 2>/dev/null | tail -1 > gpurun_out/bench_samples_n1.log
