@@ -61,7 +61,7 @@ class ClockSampler:
     """SM clock / throttle reasons of this rank's GPU, sampled during the timed region.  NVML in-process (a thread,
     started before the warm-up so that NVML's start-up cost stays outside the timed region; `mark()` drops what was
     sampled before it) — forking nvidia-smi next to the timed loop stalled the launching thread for tens of ms."""
-    PERIOD = 0.05
+    PERIOD = 0.01
 
     def __init__(self, index):
         self.index, self.rows, self.handle, self.nvml, self.running = index, [], None, None, False
@@ -408,7 +408,7 @@ def run_gpu(args):
     if world == 1 and not args.no_cpu:
         line["cpu_baseline"] = cpu_baseline(args)
     if not args.no_box:
-        box = measure(BOX_WORKLOAD, max(1, args.steps // 2), 3, False)
+        box = measure(BOX_WORKLOAD, max(1, min(5, args.steps)), 3, False)
         bc = box["counters"]
         line["box_variant"] = {"workload": f"{BOX_WORKLOAD}: dragon inside the main.py room, same size/spp/bounces",
                                "value": box["mrays_s"], "unit": "Mrays/s", "ms_per_frame": box["ms_per_step"],
@@ -449,7 +449,7 @@ def main():
         real_stdout.flush()
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--variant", default="auto", choices=["auto", "pixel", "persistent", "wavefront", "pool", "samples"])

@@ -152,8 +152,11 @@ RT_DEV f3 lerpDirPre(f3 diffuse, float k0, f3 s1) {
 #define RT_VOTE_SHADE_LANES 12
 #endif
 
+#ifndef RT_VOTE_MIN_CTAS
+#define RT_VOTE_MIN_CTAS 6
+#endif
 template <bool COUNT, bool IDS>
-__global__ void __launch_bounds__(kThreads) rtVoteKernel(const __grid_constant__ PassParams P) {
+__global__ void __launch_bounds__(kThreads, COUNT ? 1 : RT_VOTE_MIN_CTAS) rtVoteKernel(const __grid_constant__ PassParams P) {
     extern __shared__ uint2 smem[];
     const DeviceScene& sc = P.scene;
     const uint32_t lane = threadIdx.x & 31u;

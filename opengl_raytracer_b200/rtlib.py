@@ -19,7 +19,7 @@ import numpy as np
 from .configs import RenderParams
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "csrc", "librt_b200.so")
+LIB_PATH = os.environ.get("RT_B200_LIB") or os.path.join(_HERE, "csrc", "librt_b200.so")
 
 c_f3 = ctypes.c_float * 3
 
