@@ -377,18 +377,27 @@ def run_gpu(args):
                         "this rank's launch, against the measured HBM copy peak.  The scene (8 MB) is L2/L1-resident by "
                         "design, so DRAM traffic is the framebuffer only (see traffic) and the limits that bind are the "
                         "L1 data pipe (one wavefront per divergent 16-byte node load) and warp issue: see l1_wavefronts / issue"}
+    # the on-SM ceilings, micro-benchmarked on this GPU right now (csrc/rt_peaks.cu); nominal = units x clock
+    measured = ctx.measure_peaks() if rank == 0 else {}
+    roofline["measured_peaks"] = measured
     if prof.get("inst_executed_per_launch"):
-        peak_issue = sm_count * 4 * clock_mhz * 1e6
+        peak_issue = measured.get("issue_gwarpinst_s", 0.0) * 1e9 or sm_count * 4 * clock_mhz * 1e6
         ach = prof["inst_executed_per_launch"] / world / (main["kernel_ms"] * 1e-3)     # N > 1: this rank's 1/N share (approx.)
         roofline["issue"] = {"achieved": ach / 1e9, "peak": peak_issue / 1e9, "unit": "G warp-inst/s", "frac": ach / peak_issue,
-                             "lanes_per_inst": prof.get("lanes_per_inst"),
-                             "source": "inst per launch from the committed ncu capture of this workload, time live"}
+                             "lanes_per_inst": prof.get("lanes_per_inst"), "peak_nominal": sm_count * 4 * clock_mhz * 1e-3,
+                             "source": "inst per launch from the committed ncu capture of this workload, time live; "
+                                       "peak = FFMA issue micro-benchmark on this GPU (nominal: 4 schedulers x SMs x clock)"}
     if prof.get("l1_wavefronts_per_launch"):
-        peak_wf = sm_count * clock_mhz * 1e6
+        peak_wf = measured.get("l1_gwavefronts_s", 0.0) * 1e9 or sm_count * clock_mhz * 1e6
         ach = prof["l1_wavefronts_per_launch"] / world / (main["kernel_ms"] * 1e-3)
         roofline["l1_wavefronts"] = {"achieved": ach / 1e9, "peak": peak_wf / 1e9, "unit": "G wavefronts/s", "frac": ach / peak_wf,
+                                     "peak_nominal": sm_count * clock_mhz * 1e-3,
                                      "source": "l1tex data-pipe wavefronts per launch from the committed ncu capture, time live; "
-                                               "peak = 1 wavefront / cycle / SM"}
+                                               "peak = divergent-LDG.128 micro-benchmark on this GPU (nominal: 1 wavefront / cycle / SM)"}
+    if measured.get("l2_gbs"):
+        # the scene data the kernel consumes comes from L1/L2, so the L2 -> SM bandwidth is the memory ceiling to compare
+        # the algorithmic bytes with; above 1 means L1 serves the rest
+        roofline["l2"] = {"achieved": achieved, "peak": measured["l2_gbs"], "unit": "GB/s", "frac": achieved / measured["l2_gbs"]}
     line = {"metric": METRIC, "value": main["mrays_s"], "unit": "Mrays/s", "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": main["ms_per_step"], "higher_is_better": True, "scaling": "strong",
             "vs_baseline": None, "dtype": "f32", "data": "synthetic",

@@ -25,6 +25,7 @@ cudaError_t rtLaunchPersistent(const PassParams& P, bool count, bool ids, int sm
 cudaError_t rtLaunchPool(const PassParams& P, bool count, bool ids, int sms, cudaStream_t stream);
 cudaError_t rtLaunchWavefront(const PassParams& P, bool count, bool ids, int sms, cudaStream_t stream);
 cudaError_t rtLaunchSamples(const PassParams& P, bool ids, int sms, uint32_t* todoA, uint32_t* todoB, cudaStream_t stream);
+cudaError_t rtMeasurePeaks(int sms, cudaStream_t stream, double* out);
 int rtSpecRounds();
 int rtSpecLaunches();
 int rtSpecWorkUints();
@@ -666,6 +667,14 @@ int rt_read_accum_f32(rt_ctx* c, float* dst) {
 // Upload an accumulation image into the current target (checkpoint restore; the GL counterpart would be
 // glTexSubImage2D on accum_tex[accum_index], which the reference never does).
 int rt_last_pass_launches(rt_ctx* c) { return c ? c->lastLaunches : 0; }
+
+int rt_measure_peaks(rt_ctx* c, double* out3) {
+    if (!c || !out3) return RT_ERR_INVALID;
+    Bind bind(c);
+    out3[0] = out3[1] = out3[2] = 0.0;
+    RT_CUDA(c, rtMeasurePeaks(c->smCount, c->stream, out3));
+    return RT_OK;
+}
 
 int rt_write_accum_f32(rt_ctx* c, const float* src) {
     if (!c || !src) return RT_ERR_INVALID;

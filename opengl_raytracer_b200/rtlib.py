@@ -82,6 +82,7 @@ def load_library(path: str | None = None):
         "rt_set_params": (i, [vp, P(RtParams)]),
         "rt_set_variant": (i, [vp, i]),
         "rt_last_pass_launches": (i, [vp]),
+        "rt_measure_peaks": (i, [vp, P(ctypes.c_double)]),
         "rt_target_create": (i, [vp, i, i]),
         "rt_target_clear": (i, [vp]),
         "rt_target_free": (i, [vp]),
@@ -195,6 +196,12 @@ class Context:
 
     def last_pass_launches(self) -> int:
         return int(self.lib.rt_last_pass_launches(self.handle))
+
+    def measure_peaks(self) -> dict:
+        """Micro-benchmarked ceilings of this GPU: warp issue, L1 data-pipe wavefronts, L2 -> SM bandwidth."""
+        out = (ctypes.c_double * 3)()
+        self._check(self.lib.rt_measure_peaks(self.handle, out))
+        return {"issue_gwarpinst_s": out[0], "l1_gwavefronts_s": out[1], "l2_gbs": out[2]}
 
     def set_stream(self, cuda_stream: int | None):
         self._check(self.lib.rt_set_stream(self.handle, ctypes.c_void_p(cuda_stream or 0)))
