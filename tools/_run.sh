@@ -1,4 +1,4 @@
-for L in "" tools/_libs/librt_m7.so tools/_libs/librt_m8.so; do
-for C in "cfg4_open 3840 2160 64" "cfg4_box 3840 2160 8"; do
-echo -n "lib=$L "; RT_B200_LIB=$L python tools/prof_case.py $C persistent 5 1 2>&1 | tail -1
-done; done
+N=${1:-8}
+for S in cfg5_box cfg5_open; do
+python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29512 tools/bench_frames.py --scene $S --frames 1024 --repeats 2 2>gpurun_out/frames_$S_n$N.err | tail -1 | tee gpurun_out/frames_${S}_n$N.json
+done
