@@ -83,6 +83,9 @@ def test_image_ids_counters_match_oracle(ctx, oracle_mod, scene_buffers, scene, 
     ("cfg1_open", 160, 90, 4, 2, {}),
     ("cfg4_open", 192, 108, 24, 1, {}),                   # open sky: the case the variant is for
     ("cfg2_box", 96, 54, 3, 1, {}),                       # emitter + mirror sphere
+    ("cfg4_open", 96, 54, 96, 1, {}),                     # many samples: chains that run through several size classes
+    ("rects_box", 40, 24, 40, 1, {"bounces": 7}),         # 8 hits per sample: the last round's bound, a full table buffer
+    ("cfg2_box", 64, 36, 48, 2, {}),
 ])
 def test_samples_variant_matches_oracle(ctx, oracle_mod, scene_buffers, monkeypatch, scene, w, h, spp, frames, over, mode):
     """The samples variant (parallel evaluation of F(k) + per-pixel chain) without counting flags, in its device-chosen
