@@ -11,12 +11,15 @@
 // This variant keeps K rays ("slots") per lane in SHARED MEMORY (227 KB per SM on B200 is what makes it fit):
 // a lane whose ray waits for the leaf or shade stage simply steps its other ray.  Each iteration of the warp
 // runs ONE stage, picked by ballot:
-//     EXTEND  — a burst of S internal-node steps for the lane's first ray that is at an internal node; runs
-//               while at least RT_POOL_TI lanes have such a ray (so this hot stage is always densely populated);
+//     EXTEND  — a burst of S internal-node steps for the lane's first ray that is at an internal node whose record
+//               is staged in shared memory; the default stage: it runs whenever no other stage has reached its
+//               threshold (so this hot stage is the densely populated one);
+//     DEEP    — the same step for rays at nodes that must come from global memory;
 //     LEAF    — triangle tests of one waiting leaf per lane, then the pop;
 //     SHADE   — finished rays: terminal events, hit shading, next ray / next sample / next pixel (work fetched
 //               from a global counter with one warp-aggregated atomic).
-// LEAF and SHADE run when fewer than RT_POOL_TI lanes can extend, i.e. when enough rays have piled up for them.
+// SHADE, LEAF and DEEP run when RT_POOL_TS / RT_POOL_TL / RT_POOL_TD lanes have a ray waiting for them (checked in
+// that order), or when nothing else can run.  Measured outcome: profiles/r01_variants.md §5 — not what AUTO picks.
 // The first `topCount` nodes of the tree (breadth-first numbering, so: its top levels — 78-89 % of all node
 // visits with 512-1024 nodes, tools/node_hist.py) are staged in shared memory, where a divergent 16-byte read
 // costs bank conflicts instead of one L1 wavefront per lane.
