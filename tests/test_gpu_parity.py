@@ -281,3 +281,33 @@ def test_headless_app_loop_and_checkpoint(tmp_path, oracle_mod):
     assert app2.screen.read_accum().tobytes() == whole.tobytes()
     app2.save(str(tmp_path / "out.png"))
     app2.close()
+
+
+def test_scene_reupload_reuses_buffers_and_rebuilds_records(ctx, scene_buffers):
+    """rt_scene_upload keeps its device buffers and pinned staging between uploads and builds the triangle records on
+    the device: a large scene, then a small one, then the large one again must render exactly as the first time."""
+    big = scene_buffers("cfg2_box")
+    small = scene_buffers("rects_box")
+    frames = []
+    for tris, boxes, indices, cfg in (big, small, big, small):
+        params = cfg.scaled(80, 45, 2).params()
+        frames.append(_render_gpu(ctx, tris, boxes, indices, params, 1, "pixel"))
+    assert frames[0].tobytes() == frames[2].tobytes()
+    assert frames[1].tobytes() == frames[3].tobytes()
+    assert frames[0].tobytes() != frames[1].tobytes()
+
+
+def test_launch_count_and_measured_peaks(ctx, scene_buffers):
+    """The two measurement aids of the C ABI: kernels launched by the last pass, micro-benchmarked ceilings."""
+    tris, boxes, indices, cfg = scene_buffers("rects_box")
+    params = cfg.scaled(64, 36, 2).params()
+    _render_gpu(ctx, tris, boxes, indices, params, 1, "pixel")
+    assert ctx.last_pass_launches() == 1
+    _render_gpu(ctx, tris, boxes, indices, params, 1, "wavefront")
+    assert ctx.last_pass_launches() == 2
+    _render_gpu(ctx, tris, boxes, indices, params, 1, "samples")
+    assert ctx.last_pass_launches() == 12                       # stage 1 + round 0 (2) + 3 later rounds x 3
+    peaks = ctx.measure_peaks()
+    assert 100.0 < peaks["issue_gwarpinst_s"] < 3000.0           # B200 nominal: 148 SMs x 4 x 1.965 GHz = 1163
+    assert 20.0 < peaks["l1_gwavefronts_s"] < 1000.0             # nominal: 1 per cycle per SM = 291
+    assert 1000.0 < peaks["l2_gbs"] < 100000.0
