@@ -1,7 +1,4 @@
-for B in 1 8; do
-for T in tools tools/_old/tools; do
-echo "TREE=$T B=$B"
-python $T/prof_case.py cfg4_open 3840 2160 64 samples 3 $B 2>&1 | tail -1
-ncu --metrics gpu__time_duration.sum --clock-control none --csv --log-file gpurun_out/spec_ab.csv python $T/prof_case.py cfg4_open 3840 2160 64 samples 2 $B > /dev/null 2>&1
-python tools/spec_launches.py gpurun_out/spec_ab.csv
+for T in "0,0,0,0" "0,0,0,2" "0,0,0,3" "0,0,0,4" "0,0,0,5"; do
+for C in "cfg4_open 3840 2160 64" "cfg4_box 3840 2160 8"; do
+RT_VOTE_TUNE=$T python tools/prof_case.py $C persistent 4 1 2>&1 | awk '{printf "%s %s %s %s %s | ", $1, $3,$4,$5,$6} END {print ""}'
 done; done
