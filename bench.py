@@ -14,16 +14,17 @@ N > 1: tile mode — rank g owns the interleaved 8-row bands (y // 8) % N == g o
 scaling), the bands are gathered to rank 0 over NCCL inside the timed region.
 
 JSON keys beyond the contract: "roofline" (dominant kernel, algorithmic scene bytes per ray from SURVEY §8d
-against the measured HBM peak — the scene is L2-resident by design, so this is an L2/issue-bound path and the
-fraction can exceed 1; "issue" carries the warp-instruction roofline), "cpu_baseline", "box_variant" (same
-frame size with the dragon inside the reference's closed room: the realistic-throughput figure).
+against the measured HBM peak — the scene is L2-resident by design, so this is an L1/issue-bound path; its
+sub-objects "issue", "l1_wavefronts" and "l2" compare the kernel with ceilings micro-benchmarked on the same GPU
+right after the timed region, "measured_peaks"), "phases_ms" (CUDA-event split of a step: flush+clear, pass, and
+for N > 1 pack / NCCL gather / scatter), "cpu_baseline", "box_variant" (same frame size with the dragon inside
+the reference's closed room: the realistic-throughput figure).
 """
 from __future__ import annotations
 
 import argparse
 import json
 import os
-import subprocess
 import sys
 import threading
 import time
