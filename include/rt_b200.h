@@ -103,7 +103,9 @@ int rt_set_stream(rt_ctx* ctx, void* cuda_stream);
 int rt_sync(rt_ctx* ctx);
 
 /* tris: n_tris x 144 B, boxes: n_boxes x 48 B, indices: n_indices x u32 (layouts: scene.py:45-70).
- * Validates every child / offset / index, copies, and builds the device layout. */
+ * Validates every child / offset / index, copies, and builds the device layout.  The caller's arrays are free at
+ * return.  Passes already issued keep rendering the previous scene: the new one is built in a second set of buffers on
+ * a stream of its own, so a re-upload overlaps the render in flight. */
 int rt_scene_upload(rt_ctx* ctx, const void* tris, uint32_t n_tris, const void* boxes, uint32_t n_boxes,
                     const uint32_t* indices, uint32_t n_indices);
 int rt_scene_free(rt_ctx* ctx);
@@ -135,6 +137,12 @@ int rt_render_frames_sum(rt_ctx* ctx, int first_frame, int n_frames, int frame_s
 
 /* Read-backs of the current accumulation target (the one the last pass wrote). */
 int rt_read_accum_f32(rt_ctx* ctx, float* dst_rgba);        /* width*height*4 floats */
+/* The same read-back without waiting for it (glReadPixels into a pixel-buffer object): the copy runs on a stream of its
+ * own behind the passes issued so far and overlaps the next ones; dst_rgba (pinned memory, or the copy is not
+ * asynchronous) is valid after rt_read_wait.  Writers of the copied target wait for the copy on the device; a caller
+ * that writes through rt_accum_device_ptr must call rt_read_wait first. */
+int rt_read_accum_f32_async(rt_ctx* ctx, float* dst_rgba);
+int rt_read_wait(rt_ctx* ctx);
 int rt_write_accum_f32(rt_ctx* ctx, const float* src_rgba); /* checkpoint restore into the current target */
 int rt_read_rgba8(rt_ctx* ctx, uint8_t* dst_rgba);          /* round(clamp(x,0,1)*255), main.py:434 */
 int rt_read_primary_ids(rt_ctx* ctx, int32_t* dst);         /* width*height, needs RT_PASS_PRIMARY_IDS */

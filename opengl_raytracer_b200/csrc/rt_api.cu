@@ -45,15 +45,25 @@ struct rt_ctx {
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
     std::string err;
     // scene
-    NodeRec* dNodes = nullptr;
-    TriRec* dTris = nullptr;
-    ShadeRec* dShade = nullptr;
-    uint32_t* dTriId = nullptr;
-    uint2* dBig = nullptr;
-    float4* dRawTris = nullptr;           // the caller's tris[] as uploaded (144 B each); records are built from it on the device
-    size_t capNodes = 0, capSlots = 0, capSlotRecs = 0, capBig = 0, capRaw = 0;   // element capacities: re-uploads reuse the buffers
-    void* hStage = nullptr;               // pinned staging for nodes + slot ids + big leaves
-    size_t hStageBytes = 0;
+    // Two sets of scene buffers: an upload fills the set that is NOT in use, on its own stream, while passes already
+    // launched keep reading the other one (they hold its pointers by value) — a re-upload overlaps the previous render.
+    struct SceneSet {
+        NodeRec* dNodes = nullptr;
+        TriRec* dTris = nullptr;
+        ShadeRec* dShade = nullptr;
+        uint32_t* dTriId = nullptr;
+        uint2* dBig = nullptr;
+        float4* dRawTris = nullptr;       // the caller's tris[] as uploaded (144 B each); records are built from it on the device
+        size_t capNodes = 0, capSlots = 0, capSlotRecs = 0, capBig = 0, capRaw = 0;   // element capacities: re-uploads reuse the buffers
+        void* hStage = nullptr;           // pinned staging for nodes + slot ids + big leaves
+        size_t hStageBytes = 0;
+        cudaEvent_t lastUse = nullptr;    // recorded after every pass that reads this set
+    } sets[2];
+    int curSet = 0;
+    cudaStream_t upStream = nullptr, downStream = nullptr;   // H2D of an upload / D2H of an asynchronous read-back
+    cudaEvent_t evRendered = nullptr;                        // main stream -> downStream
+    cudaEvent_t evDown[2] = {nullptr, nullptr};              // read-back of target[i] finished (awaited before target[i] is written)
+    bool downPending[2] = {false, false};
     DeviceScene scene{};
     bool haveScene = false;
     // uniforms
@@ -132,13 +142,24 @@ struct HostBox {
 static_assert(sizeof(HostTri) == 144 && sizeof(HostBox) == 48, "std430 layout");
 
 void freeScene(rt_ctx* c) {
-    cudaFree(c->dNodes); cudaFree(c->dTris); cudaFree(c->dShade); cudaFree(c->dTriId); cudaFree(c->dBig);
-    cudaFree(c->dRawTris); cudaFreeHost(c->hStage);
-    c->dNodes = nullptr; c->dTris = nullptr; c->dShade = nullptr; c->dTriId = nullptr; c->dBig = nullptr;
-    c->dRawTris = nullptr; c->hStage = nullptr;
-    c->capNodes = c->capSlots = c->capSlotRecs = c->capBig = c->capRaw = c->hStageBytes = 0;
+    for (auto& S : c->sets) {
+        cudaFree(S.dNodes); cudaFree(S.dTris); cudaFree(S.dShade); cudaFree(S.dTriId); cudaFree(S.dBig);
+        cudaFree(S.dRawTris); cudaFreeHost(S.hStage);
+        S.dNodes = nullptr; S.dTris = nullptr; S.dShade = nullptr; S.dTriId = nullptr; S.dBig = nullptr;
+        S.dRawTris = nullptr; S.hStage = nullptr;
+        S.capNodes = S.capSlots = S.capSlotRecs = S.capBig = S.capRaw = S.hStageBytes = 0;
+    }
     c->haveScene = false;
     c->scene = DeviceScene{};
+}
+
+// Main-stream work that writes an accumulation target first waits for read-backs still copying out of it.
+void waitDownloads(rt_ctx* c, int which = -1) {      // which: target 0 / 1, or -1 for both
+    for (int i = 0; i < 2; i++)
+        if ((which < 0 || which == i) && c->downPending[i]) {
+            cudaStreamWaitEvent(c->stream, c->evDown[i], 0);
+            c->downPending[i] = false;
+        }
 }
 
 void freeQueue(rt_ctx* c) {
@@ -246,6 +267,13 @@ int rt_create(rt_ctx** out, int device) {
     if (cudaGetDeviceProperties(&prop, device) != cudaSuccess) { delete c; return RT_ERR_CUDA; }
     c->smCount = prop.multiProcessorCount;
     if (cudaStreamCreateWithFlags(&c->ownStream, cudaStreamNonBlocking) != cudaSuccess ||
+        cudaStreamCreateWithFlags(&c->upStream, cudaStreamNonBlocking) != cudaSuccess ||
+        cudaStreamCreateWithFlags(&c->downStream, cudaStreamNonBlocking) != cudaSuccess ||
+        cudaEventCreateWithFlags(&c->evRendered, cudaEventDisableTiming) != cudaSuccess ||
+        cudaEventCreateWithFlags(&c->evDown[0], cudaEventDisableTiming) != cudaSuccess ||
+        cudaEventCreateWithFlags(&c->evDown[1], cudaEventDisableTiming) != cudaSuccess ||
+        cudaEventCreateWithFlags(&c->sets[0].lastUse, cudaEventDisableTiming) != cudaSuccess ||
+        cudaEventCreateWithFlags(&c->sets[1].lastUse, cudaEventDisableTiming) != cudaSuccess ||
         cudaEventCreate(&c->ev0) != cudaSuccess || cudaEventCreate(&c->ev1) != cudaSuccess ||
         cudaMalloc(&c->dCounters, RT_CNT_COUNT * sizeof(unsigned long long)) != cudaSuccess ||
         cudaMalloc(&c->dWork, sizeof(unsigned int)) != cudaSuccess ||
@@ -264,12 +292,15 @@ void rt_destroy(rt_ctx* c) {
     if (!c) return;
     Bind bind(c);
     cudaStreamSynchronize(c->stream);
+    if (c->upStream) cudaStreamSynchronize(c->upStream);
+    if (c->downStream) cudaStreamSynchronize(c->downStream);
     freeScene(c);
     freeTargets(c);
     cudaFree(c->dCounters); cudaFree(c->dWork); cudaFree(c->dQueueCount); cudaFree(c->dWorkArr);
-    if (c->ev0) cudaEventDestroy(c->ev0);
-    if (c->ev1) cudaEventDestroy(c->ev1);
-    if (c->ownStream) cudaStreamDestroy(c->ownStream);
+    for (cudaEvent_t e : {c->ev0, c->ev1, c->evRendered, c->evDown[0], c->evDown[1], c->sets[0].lastUse, c->sets[1].lastUse})
+        if (e) cudaEventDestroy(e);
+    for (cudaStream_t st : {c->ownStream, c->upStream, c->downStream})
+        if (st) cudaStreamDestroy(st);
     delete c;
 }
 
@@ -414,11 +445,13 @@ int rt_scene_upload(rt_ctx* c, const void* trisV, uint32_t nTris, const void* bo
         }
     }
 
-    // device side: buffers are reused while they are large enough (a re-upload then costs no allocation); the three small
-    // tables go through one pinned staging block, the caller's tris[] is copied as it is and the 48 B + 80 B records of
-    // every slot are built from it by a kernel (same operations, same order, no contraction: fragment.glsl:112-116)
-    RT_CUDA(c, cudaStreamSynchronize(c->stream));     // passes in flight still read the old scene
-    c->haveScene = false;
+    // device side: the set of buffers that is not in use is filled on the upload stream, so passes still in flight on the
+    // main stream (they read the other set) are not waited for.  Buffers are reused while they are large enough (a
+    // re-upload then costs no allocation); the three small tables go through one pinned staging block, the caller's
+    // tris[] is copied as it is and the 48 B + 80 B records of every slot are built from it by a kernel (same operations,
+    // same order, no contraction: fragment.glsl:112-116).
+    rt_ctx::SceneSet& S = c->sets[c->curSet ^ 1];
+    RT_CUDA(c, cudaEventSynchronize(S.lastUse));      // passes that read this set two uploads ago
     auto grow = [&](auto** ptr, size_t& cap, size_t need) -> cudaError_t {
         using T = typename std::remove_pointer<typename std::remove_pointer<decltype(ptr)>::type>::type;
         if (need <= cap && *ptr) return cudaSuccess;
@@ -429,36 +462,40 @@ int rt_scene_upload(rt_ctx* c, const void* trisV, uint32_t nTris, const void* bo
         return e;
     };
     const size_t nSlotsAll = triIds.size();
-    RT_CUDA(c, grow(&c->dNodes, c->capNodes, nodes.size()));
-    RT_CUDA(c, grow(&c->dTriId, c->capSlots, nSlotsAll));
-    if (!c->dTris || !c->dShade || c->capSlots != c->capSlotRecs) {
-        cudaFree(c->dTris); cudaFree(c->dShade); c->dTris = nullptr; c->dShade = nullptr; c->capSlotRecs = 0;
-        RT_CUDA(c, cudaMalloc(reinterpret_cast<void**>(&c->dTris), c->capSlots * sizeof(TriRec)));
-        RT_CUDA(c, cudaMalloc(reinterpret_cast<void**>(&c->dShade), c->capSlots * sizeof(ShadeRec)));
-        c->capSlotRecs = c->capSlots;
+    RT_CUDA(c, grow(&S.dNodes, S.capNodes, nodes.size()));
+    RT_CUDA(c, grow(&S.dTriId, S.capSlots, nSlotsAll));
+    if (!S.dTris || !S.dShade || S.capSlots != S.capSlotRecs) {
+        cudaFree(S.dTris); cudaFree(S.dShade); S.dTris = nullptr; S.dShade = nullptr; S.capSlotRecs = 0;
+        RT_CUDA(c, cudaMalloc(reinterpret_cast<void**>(&S.dTris), S.capSlots * sizeof(TriRec)));
+        RT_CUDA(c, cudaMalloc(reinterpret_cast<void**>(&S.dShade), S.capSlots * sizeof(ShadeRec)));
+        S.capSlotRecs = S.capSlots;
     }
-    RT_CUDA(c, grow(&c->dBig, c->capBig, bigLeaves.size()));
-    RT_CUDA(c, grow(&c->dRawTris, c->capRaw, size_t(nTris) * (sizeof(HostTri) / sizeof(float4))));
+    RT_CUDA(c, grow(&S.dBig, S.capBig, bigLeaves.size()));
+    RT_CUDA(c, grow(&S.dRawTris, S.capRaw, size_t(nTris) * (sizeof(HostTri) / sizeof(float4))));
     const size_t bytesNodes = nodes.size() * sizeof(NodeRec), bytesIds = nSlotsAll * sizeof(uint32_t),
                  bytesBig = bigLeaves.size() * sizeof(uint2);
     const size_t offIds = bytesNodes, offBig = (offIds + bytesIds + 15) & ~size_t(15), stageBytes = offBig + bytesBig;
-    if (stageBytes > c->hStageBytes) {
-        cudaFreeHost(c->hStage); c->hStage = nullptr; c->hStageBytes = 0;
-        RT_CUDA(c, cudaMallocHost(&c->hStage, stageBytes + stageBytes / 8));
-        c->hStageBytes = stageBytes + stageBytes / 8;
+    if (stageBytes > S.hStageBytes) {
+        cudaFreeHost(S.hStage); S.hStage = nullptr; S.hStageBytes = 0;
+        RT_CUDA(c, cudaMallocHost(&S.hStage, stageBytes + stageBytes / 8));
+        S.hStageBytes = stageBytes + stageBytes / 8;
     }
-    char* stage = static_cast<char*>(c->hStage);
+    char* stage = static_cast<char*>(S.hStage);
     if (bytesNodes) std::memcpy(stage, nodes.data(), bytesNodes);
     if (bytesIds) std::memcpy(stage + offIds, triIds.data(), bytesIds);
     if (bytesBig) std::memcpy(stage + offBig, bigLeaves.data(), bytesBig);
-    if (nTris) RT_CUDA(c, cudaMemcpyAsync(c->dRawTris, tris, size_t(nTris) * sizeof(HostTri), cudaMemcpyHostToDevice, c->stream));
-    if (bytesNodes) RT_CUDA(c, cudaMemcpyAsync(c->dNodes, stage, bytesNodes, cudaMemcpyHostToDevice, c->stream));
-    if (bytesIds) RT_CUDA(c, cudaMemcpyAsync(c->dTriId, stage + offIds, bytesIds, cudaMemcpyHostToDevice, c->stream));
-    if (bytesBig) RT_CUDA(c, cudaMemcpyAsync(c->dBig, stage + offBig, bytesBig, cudaMemcpyHostToDevice, c->stream));
+    cudaStream_t up = c->upStream;
+    if (nTris) RT_CUDA(c, cudaMemcpyAsync(S.dRawTris, tris, size_t(nTris) * sizeof(HostTri), cudaMemcpyHostToDevice, up));
+    if (bytesNodes) RT_CUDA(c, cudaMemcpyAsync(S.dNodes, stage, bytesNodes, cudaMemcpyHostToDevice, up));
+    if (bytesIds) RT_CUDA(c, cudaMemcpyAsync(S.dTriId, stage + offIds, bytesIds, cudaMemcpyHostToDevice, up));
+    if (bytesBig) RT_CUDA(c, cudaMemcpyAsync(S.dBig, stage + offBig, bytesBig, cudaMemcpyHostToDevice, up));
     if (nSlotsAll)
-        RT_CUDA(c, rtLaunchBuildRecords(c->dRawTris, c->dTriId, uint32_t(nSlotsAll), c->dTris, c->dShade, c->stream));
-    RT_CUDA(c, cudaStreamSynchronize(c->stream));     // glBufferData semantics: the caller's arrays are free at return
-    sc.nodes = c->dNodes; sc.tris = c->dTris; sc.shade = c->dShade; sc.triId = c->dTriId; sc.bigLeaves = c->dBig;
+        RT_CUDA(c, rtLaunchBuildRecords(S.dRawTris, S.dTriId, uint32_t(nSlotsAll), S.dTris, S.dShade, up));
+    // glBufferData semantics: the caller's arrays are free at return; and every later launch on the main stream is
+    // issued after this point, so it sees the finished set
+    RT_CUDA(c, cudaStreamSynchronize(up));
+    c->curSet ^= 1;
+    sc.nodes = S.dNodes; sc.tris = S.dTris; sc.shade = S.dShade; sc.triId = S.dTriId; sc.bigLeaves = S.dBig;
     sc.nNodes = uint32_t(nodes.size());
     sc.nSlots = uint32_t(nSlotsAll);
     c->scene = sc;
@@ -487,6 +524,8 @@ int rt_target_free(rt_ctx* c) {
     if (!c) return RT_ERR_INVALID;
     Bind bind(c);
     cudaStreamSynchronize(c->stream);
+    cudaStreamSynchronize(c->downStream);
+    c->downPending[0] = c->downPending[1] = false;
     freeTargets(c);
     return RT_OK;
 }
@@ -495,6 +534,7 @@ int rt_target_clear(rt_ctx* c) {
     if (!c) return RT_ERR_INVALID;
     if (!c->target[0]) return fail(c, RT_ERR_STATE, "no target");
     Bind bind(c);
+    waitDownloads(c);
     const size_t n = size_t(c->width) * c->height;
     RT_CUDA(c, cudaMemsetAsync(c->target[0], 0, n * sizeof(float4), c->stream));
     RT_CUDA(c, cudaMemsetAsync(c->target[1], 0, n * sizeof(float4), c->stream));
@@ -508,6 +548,8 @@ int rt_target_create(rt_ctx* c, int width, int height) {
     if (width <= 0 || height <= 0) return fail(c, RT_ERR_INVALID, "target size %d x %d", width, height);
     Bind bind(c);
     cudaStreamSynchronize(c->stream);
+    cudaStreamSynchronize(c->downStream);
+    c->downPending[0] = c->downPending[1] = false;
     freeTargets(c);
     const size_t n = size_t(width) * height;
     if (cudaMalloc(&c->target[0], n * sizeof(float4)) != cudaSuccess || cudaMalloc(&c->target[1], n * sizeof(float4)) != cudaSuccess ||
@@ -530,6 +572,7 @@ int renderPass(rt_ctx* c, int frameNumber, int tileX, int tileY, int flags, int 
     if (!c->haveScene) return fail(c, RT_ERR_STATE, "rt_render_pass before rt_scene_upload");
     if (!c->haveParams) return fail(c, RT_ERR_STATE, "rt_render_pass before rt_set_params");
     if (!c->target[0]) return fail(c, RT_ERR_STATE, "rt_render_pass before rt_target_create");
+    waitDownloads(c, 1 - c->accumIndex);                 // the target this pass writes
     const rt_params& u = c->params;
     PassParams P{};
     P.scene = c->scene;
@@ -598,6 +641,7 @@ int renderPass(rt_ctx* c, int frameNumber, int tileX, int tileY, int flags, int 
         e = rtLaunchPixel(P, P.counters != nullptr, P.primaryIds != nullptr, c->stream);
     if (e != cudaSuccess) return fail(c, RT_ERR_CUDA, "kernel launch: %s", cudaGetErrorString(e));
     c->lastLaunches = variant == RT_VARIANT_SAMPLES ? rtSpecLaunches() : variant == RT_VARIANT_WAVEFRONT ? 2 : 1;
+    cudaEventRecord(c->sets[c->curSet].lastUse, c->stream);     // the next upload into this set waits for it
     c->accumIndex = next;
     return RT_OK;
 }
@@ -650,18 +694,38 @@ int rt_finish_sum(rt_ctx* c, int totalFrames) {
     if (!c->target[0]) return fail(c, RT_ERR_STATE, "no target");
     if (totalFrames <= 0) return fail(c, RT_ERR_INVALID, "total_frames must be positive");
     Bind bind(c);
+    waitDownloads(c, c->accumIndex);
     RT_CUDA(c, rtLaunchFinishSum(c->target[c->accumIndex], size_t(c->width) * c->height, float(totalFrames), c->stream));
     return RT_OK;
 }
 
-int rt_read_accum_f32(rt_ctx* c, float* dst) {
+// The read-back runs on its own stream behind everything the main stream has been given so far, so the next passes
+// overlap it (the GL counterpart is glReadPixels into a pixel-buffer object); a pass that is about to overwrite the
+// target being copied waits for the copy on the device (waitDownloads), never on the host.
+int rt_read_accum_f32_async(rt_ctx* c, float* dst) {
     if (!c || !dst) return RT_ERR_INVALID;
     if (!c->target[0]) return fail(c, RT_ERR_STATE, "no target");
     Bind bind(c);
-    RT_CUDA(c, cudaMemcpyAsync(dst, c->target[c->accumIndex], size_t(c->width) * c->height * sizeof(float4),
-                               cudaMemcpyDeviceToHost, c->stream));
-    RT_CUDA(c, cudaStreamSynchronize(c->stream));
+    const int idx = c->accumIndex;
+    RT_CUDA(c, cudaEventRecord(c->evRendered, c->stream));
+    RT_CUDA(c, cudaStreamWaitEvent(c->downStream, c->evRendered, 0));
+    RT_CUDA(c, cudaMemcpyAsync(dst, c->target[idx], size_t(c->width) * c->height * sizeof(float4), cudaMemcpyDeviceToHost,
+                               c->downStream));
+    RT_CUDA(c, cudaEventRecord(c->evDown[idx], c->downStream));
+    c->downPending[idx] = true;
     return RT_OK;
+}
+
+int rt_read_wait(rt_ctx* c) {
+    if (!c) return RT_ERR_INVALID;
+    Bind bind(c);
+    RT_CUDA(c, cudaStreamSynchronize(c->downStream));
+    return RT_OK;
+}
+
+int rt_read_accum_f32(rt_ctx* c, float* dst) {
+    const int rc = rt_read_accum_f32_async(c, dst);
+    return rc != RT_OK ? rc : rt_read_wait(c);
 }
 
 // Upload an accumulation image into the current target (checkpoint restore; the GL counterpart would be
@@ -680,6 +744,7 @@ int rt_write_accum_f32(rt_ctx* c, const float* src) {
     if (!c || !src) return RT_ERR_INVALID;
     if (!c->target[0]) return fail(c, RT_ERR_STATE, "no target");
     Bind bind(c);
+    waitDownloads(c, c->accumIndex);
     RT_CUDA(c, cudaMemcpyAsync(c->target[c->accumIndex], src, size_t(c->width) * c->height * sizeof(float4),
                                cudaMemcpyHostToDevice, c->stream));
     RT_CUDA(c, cudaStreamSynchronize(c->stream));
@@ -747,6 +812,7 @@ static int bandCopy(rt_ctx* c, int tileY, void* dense, int toDense) {
     if (!c || !dense) return RT_ERR_INVALID;
     if (!c->haveParams || !c->target[0]) return fail(c, RT_ERR_STATE, "band copy needs params and a target");
     Bind bind(c);
+    if (!toDense) waitDownloads(c, c->accumIndex);
     const int rows = ownedCount(c->height, c->params.tileSizeY, c->params.numTilesY, tileY);
     RT_CUDA(c, rtLaunchBandCopy(c->target[c->accumIndex], static_cast<float4*>(dense), c->width, rows, c->params.tileSizeY,
                                 c->params.numTilesY, tileY, toDense, c->stream));

@@ -92,6 +92,8 @@ def load_library(path: str | None = None):
         "rt_render_frames_sum": (i, [vp, i, i, i]),
         "rt_read_accum_f32": (i, [vp, vp]),
         "rt_write_accum_f32": (i, [vp, vp]),
+        "rt_read_accum_f32_async": (i, [vp, vp]),
+        "rt_read_wait": (i, [vp]),
         "rt_read_rgba8": (i, [vp, vp]),
         "rt_read_primary_ids": (i, [vp, vp]),
         "rt_read_counters": (i, [vp, vp, i]),
@@ -240,6 +242,14 @@ class Context:
             out = np.empty((self.height, self.width, 4), dtype=np.float32)
         self._check(self.lib.rt_read_accum_f32(self.handle, out.ctypes.data))
         return out
+
+    def read_accum_f32_async(self, host_ptr: int):
+        """Start the read-back of the current target into pinned host memory at ``host_ptr`` (width*height*16 bytes);
+        passes issued afterwards overlap it.  ``read_wait()`` returns when every started read-back has landed."""
+        self._check(self.lib.rt_read_accum_f32_async(self.handle, ctypes.c_void_p(host_ptr)))
+
+    def read_wait(self):
+        self._check(self.lib.rt_read_wait(self.handle))
 
     def write_accum_f32(self, image: np.ndarray):
         """Upload an (H, W, 4) float32 accumulation into the current target (checkpoint restore)."""

@@ -311,3 +311,36 @@ def test_launch_count_and_measured_peaks(ctx, scene_buffers):
     assert 100.0 < peaks["issue_gwarpinst_s"] < 3000.0           # B200 nominal: 148 SMs x 4 x 1.965 GHz = 1163
     assert 20.0 < peaks["l1_gwavefronts_s"] < 1000.0             # nominal: 1 per cycle per SM = 291
     assert 1000.0 < peaks["l2_gbs"] < 100000.0
+
+
+def test_async_readback_and_upload_overlap_keep_results(ctx, scene_buffers):
+    """rt_read_accum_f32_async copies on its own stream while later passes run, and rt_scene_upload builds the next
+    scene in the second buffer set while a pass still reads the first: both must leave every result untouched."""
+    import torch
+    big = scene_buffers("cfg2_box")
+    small = scene_buffers("rects_box")
+    w, h = 320, 180
+    p_big, p_small = big[3].scaled(w, h, 6).params(), small[3].scaled(w, h, 6).params()
+    want_big = [None, None]
+    ctx.set_variant("auto")
+    ctx.scene_upload(*big[:3]); ctx.set_params(p_big); ctx.target_create(w, h)
+    ctx.render_pass(0, 0, 0); want_big[0] = ctx.read_accum_f32()
+    ctx.render_pass(1, 0, 0); want_big[1] = ctx.read_accum_f32()
+    ctx.scene_upload(*small[:3]); ctx.set_params(p_small); ctx.target_clear()
+    ctx.render_pass(0, 0, 0); want_small = ctx.read_accum_f32()
+
+    bufs = [torch.empty((h, w, 4), dtype=torch.float32).pin_memory() for _ in range(3)]
+    ctx.scene_upload(*big[:3]); ctx.set_params(p_big); ctx.target_clear()
+    ctx.render_pass(0, 0, 0)
+    ctx.read_accum_f32_async(bufs[0].data_ptr())           # copy of frame 0 ...
+    ctx.render_pass(1, 0, 0)                               # ... while frame 1 renders into the other target
+    ctx.read_accum_f32_async(bufs[1].data_ptr())
+    ctx.scene_upload(*small[:3])                           # next scene uploaded while frame 1 may still be in flight
+    ctx.set_params(p_small)
+    ctx.target_clear()                                     # must wait (on the device) for both copies
+    ctx.render_pass(0, 0, 0)
+    ctx.read_accum_f32_async(bufs[2].data_ptr())
+    ctx.read_wait()
+    assert bufs[0].numpy().tobytes() == want_big[0].tobytes()
+    assert bufs[1].numpy().tobytes() == want_big[1].tobytes()
+    assert bufs[2].numpy().tobytes() == want_small.tobytes()
