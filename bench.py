@@ -325,7 +325,7 @@ def run_gpu(args):
                "mrays_s": total["rays_traced"] / (ms_step * 1e-3) / 1e6,
                "ref_equiv_mrays_s": total["rays"] / (ms_step * 1e-3) / 1e6, "clocks": clocks,
                "local_alg_bytes": local_alg_bytes, "launches": steps, "phases_ms": phases,
-               "pass_launches": ctx.last_pass_launches()}   # traversal-kernel passes; the caller multiplies by kernels per pass
+               "pass_launches": ctx.last_pass_launches(), "variant": ctx.last_pass_variant()}   # traversal-kernel passes; the caller multiplies by kernels per pass
         if with_e2e:
             # end to end through the C ABI with HOST buffers: every step uploads the scene (H2D from pinned memory),
             # sets the uniforms, draws, gathers, and reads the RGBA32F frame back on rank 0 (D2H into pinned memory).
@@ -372,11 +372,8 @@ def run_gpu(args):
     fb_bytes = 16.0 * cfg.width * cfg.height / world
     alg_bytes = main["local_alg_bytes"] + fb_bytes
     achieved = alg_bytes / (main["kernel_ms"] * 1e-3) / 1e9
-    variant = args.variant
     sm_count = torch.cuda.get_device_properties(dev).multi_processor_count
-    if variant == "auto":
-        owned = cfg.width * cfg.height // world                                   # rt_api.cu renderPass()
-        variant = "pixel" if cfg.rays_per_pixel < 16 else ("persistent" if owned > sm_count * 2048 * 16 else "samples")
+    variant = main["variant"]          # what the library ran (under AUTO the device may have made the choice)
     kernel = {"pixel": "rtPixelKernel", "persistent": "vote::rtVoteKernel", "pool": "pool::rtPoolKernel",
               "wavefront": "wave::rtPrimaryKernel + wave::rtPathKernel",
               "samples": "spec::rtSpecPrimaryKernel + rounds of spec::rtSpecEvalKernel / spec::rtSpecChainKernel"}[variant]
@@ -437,6 +434,7 @@ def run_gpu(args):
         box = measure(BOX_WORKLOAD, max(1, min(5, args.steps)), 3, False)
         bc = box["counters"]
         line["box_variant"] = {"workload": f"{BOX_WORKLOAD}: dragon inside the main.py room, same size/spp/bounces",
+                               "variant": box["variant"],
                                "value": box["mrays_s"], "unit": "Mrays/s", "ms_per_frame": box["ms_per_step"],
                                "rays_per_step": bc["rays_traced"], "kernel_ms": box["kernel_ms"],
                                "roofline_achieved_gbs": (box["local_alg_bytes"] + fb_bytes) / (box["kernel_ms"] * 1e-3) / 1e9,

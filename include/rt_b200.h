@@ -114,6 +114,9 @@ int rt_set_params(rt_ctx* ctx, const rt_params* params);
 int rt_set_variant(rt_ctx* ctx, int variant);
 /* Kernels the last rt_render_pass launched (1 for the single-kernel variants; AUTO may pick a multi-stage one). */
 int rt_last_pass_launches(rt_ctx* ctx);
+/* The variant (RT_VARIANT_*) that rendered the last pass; under AUTO the choice can be made on the device, in which case
+ * this call waits for the pass. */
+int rt_last_pass_variant(rt_ctx* ctx);
 /* Measurement aid (no published peak exists for the on-SM ceilings): runs three micro-benchmarks on the
  * context's GPU and returns out3 = { G warp-instructions/s issued, G L1 data-pipe wavefronts/s, L2->SM GB/s }. */
 int rt_measure_peaks(rt_ctx* ctx, double* out3);

@@ -95,6 +95,10 @@ struct rt_ctx {
     uint32_t* dTodo[2] = {nullptr, nullptr};
     uint32_t* dChainClass = nullptr;
     int lastLaunches = 0;                 // kernel launches of the last pass (rt_last_pass_launches)
+    int lastVariant = 0;                  // what the last pass ran (rt_last_pass_variant)
+    bool lastGated = false;
+    long long lastOwned = 0;
+    uint32_t lastCapacity = 0;
     uint32_t* dChainK = nullptr;
     float4* dChainColor = nullptr;
 };
@@ -314,6 +318,7 @@ int rt_sync(rt_ctx* c) {
     if (!c) return RT_ERR_INVALID;
     Bind bind(c);
     RT_CUDA(c, cudaStreamSynchronize(c->stream));
+    RT_CUDA(c, cudaStreamSynchronize(c->downStream));     // read-backs started with rt_read_accum_f32_async
     return RT_OK;
 }
 
@@ -321,6 +326,7 @@ int rt_scene_free(rt_ctx* c) {
     if (!c) return RT_ERR_INVALID;
     Bind bind(c);
     cudaStreamSynchronize(c->stream);
+    cudaStreamSynchronize(c->upStream);
     freeScene(c);
     return RT_OK;
 }
@@ -601,16 +607,23 @@ int renderPass(rt_ctx* c, int frameNumber, int tileX, int tileY, int flags, int 
     }
     cudaError_t e;
     int variant = c->variant;
-    // AUTO, by measurement on B200 (profiles/r01_variants.md).  Few samples per pixel: the one-thread-per-pixel
-    // kernel.  Many samples per pixel make the per-pixel work uneven (sky pixels finish at once, surface pixels run
-    // rays_per_pixel paths): the persistent warp-vote kernel, as long as this GPU owns enough pixels to stay
-    // throughput-bound; when its share of the frame is small (tile-sharded frame on several GPUs) the serial sample
-    // chain of a pixel bounds the pass and the samples variant, which evaluates the samples in parallel, wins
-    // (dragon 4K 64 spp, this GPU's share 1 / 1/2 / 1/4 / 1/8: persistent 27.3 / 16.5 / 14.0 / 12.5 ms, samples
-    // 31.9 / 16.6 / 9.2 / 5.2 ms).
+    // AUTO, by measurement on B200 (profiles/r01_variants.md).  Fewer than 8 samples per pixel: the one-thread-per-pixel
+    // kernel.  More make the per-pixel work uneven (sky pixels finish at once, surface pixels run rays_per_pixel paths):
+    // the persistent warp-vote kernel.  When this GPU's share of the frame is small (a tile-sharded frame on several
+    // GPUs, or a small frame) the serial sample chain of a pixel bounds the pass, and where the sky is visible the samples
+    // variant, which evaluates the samples in parallel, wins (dragon 4K 64 spp, share 1 / 1/2 / 1/4 / 1/8: persistent
+    // 27.3 / 16.5 / 14.0 / 12.5 ms, samples 31.9 / 16.4 / 8.9 / 4.8 ms) — but in a closed room, or where many pixels
+    // hit, it loses (1080p 16 spp: 18.5 vs 10.4 ms open, 145 vs 121 ms boxed).  Which case it is only the primary rays
+    // tell, so the pass is launched with BOTH branches and stage 1's count decides on the device (specGate).
+    bool gated = false;
     if (variant == RT_VARIANT_AUTO) {
         const long long owned = (long long)P.ownedW * P.ownedH, manyPixels = (long long)c->smCount * 2048 * 16;
-        variant = u.rays_per_pixel < 16 ? RT_VARIANT_PIXEL : (owned > manyPixels ? RT_VARIANT_PERSISTENT : RT_VARIANT_SAMPLES);
+        variant = u.rays_per_pixel < 8 ? RT_VARIANT_PIXEL : RT_VARIANT_PERSISTENT;
+        if (u.rays_per_pixel >= 16 && owned <= manyPixels && P.counters == nullptr && c->width <= 65535 && c->height <= 65535 &&
+            sumMode == 0) {
+            variant = RT_VARIANT_SAMPLES;
+            gated = true;
+        }
     }
     // the samples variant evaluates paths the reference would not (speculation): it has no counting instantiation
     if (variant == RT_VARIANT_SAMPLES && (P.counters != nullptr || c->width > 65535 || c->height > 65535))
@@ -626,7 +639,9 @@ int renderPass(rt_ctx* c, int frameNumber, int tileX, int tileY, int flags, int 
         P.specBufEntries = uint32_t(std::min<size_t>(c->specBufEntries, 0xffffffffu));
         P.workCounters = c->dWorkArr; P.todoCount = c->dWorkArr + 32; P.classCount = c->dWorkArr + 64;
         P.chainK = c->dChainK; P.chainColor = c->dChainColor; P.chainClass = c->dChainClass;
+        P.specGate = gated ? 1 : 0;
         e = rtLaunchSamples(P, P.primaryIds != nullptr, c->smCount, c->dTodo[0], c->dTodo[1], c->stream);
+        if (e == cudaSuccess && gated) e = rtLaunchPersistent(P, false, P.primaryIds != nullptr, c->smCount, c->stream);
     } else if (variant == RT_VARIANT_WAVEFRONT) {
         e = ensureQueue(c, P.counters != nullptr);
         if (e != cudaSuccess) return fail(c, RT_ERR_NOMEM, "wavefront queue: %s", cudaGetErrorString(e));
@@ -640,7 +655,9 @@ int renderPass(rt_ctx* c, int frameNumber, int tileX, int tileY, int flags, int 
     else
         e = rtLaunchPixel(P, P.counters != nullptr, P.primaryIds != nullptr, c->stream);
     if (e != cudaSuccess) return fail(c, RT_ERR_CUDA, "kernel launch: %s", cudaGetErrorString(e));
-    c->lastLaunches = variant == RT_VARIANT_SAMPLES ? rtSpecLaunches() : variant == RT_VARIANT_WAVEFRONT ? 2 : 1;
+    c->lastLaunches = variant == RT_VARIANT_SAMPLES ? rtSpecLaunches() + (gated ? 1 : 0) : variant == RT_VARIANT_WAVEFRONT ? 2 : 1;
+    c->lastVariant = variant; c->lastGated = gated;
+    c->lastOwned = (long long)P.ownedW * P.ownedH; c->lastCapacity = P.specCapacity;
     cudaEventRecord(c->sets[c->curSet].lastUse, c->stream);     // the next upload into this set waits for it
     c->accumIndex = next;
     return RT_OK;
@@ -731,6 +748,21 @@ int rt_read_accum_f32(rt_ctx* c, float* dst) {
 // Upload an accumulation image into the current target (checkpoint restore; the GL counterpart would be
 // glTexSubImage2D on accum_tex[accum_index], which the reference never does).
 int rt_last_pass_launches(rt_ctx* c) { return c ? c->lastLaunches : 0; }
+
+// Which variant rendered the last pass.  Where AUTO launched both branches this reads stage 1's count back (it waits for
+// the pass) and repeats the device's decision (vote::samplesSpeculate).
+int rt_last_pass_variant(rt_ctx* c) {
+    if (!c) return RT_ERR_INVALID;
+    if (!c->lastGated) return c->lastVariant;
+    Bind bind(c);
+    unsigned int queued = 0;
+    RT_CUDA(c, cudaMemcpyAsync(&queued, c->dQueueCount, sizeof queued, cudaMemcpyDeviceToHost, c->stream));
+    RT_CUDA(c, cudaStreamSynchronize(c->stream));
+    int forced = 0, t0 = 0, t1 = 0;
+    if (const char* v = getenv("RT_VOTE_TUNE")) sscanf(v, "%d,%d,%d", &t0, &t1, &forced);
+    const bool speculate = queued <= c->lastCapacity && (forced == 1 || (forced != 2 && 4ll * queued <= c->lastOwned));
+    return speculate ? RT_VARIANT_SAMPLES : RT_VARIANT_PERSISTENT;
+}
 
 int rt_measure_peaks(rt_ctx* c, double* out3) {
     if (!c || !out3) return RT_ERR_INVALID;

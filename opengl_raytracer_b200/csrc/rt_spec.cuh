@@ -21,8 +21,9 @@
 //                                 pixel.  A chain that leaves the table continues by evaluating F on demand.
 // Cost: F is evaluated for every k < K but only every hits-th is used, so the work grows by the mean hit count per
 // path: 1.07 under open sky (worth it: the frame becomes embarrassingly parallel), 4.7 in a closed room (not worth
-// it).  The mode is decided ON THE DEVICE from stage 1's hit fraction: when more than half of the pixels hit,
-// stage 2 exits at once and stage 3 evaluates every sample on demand — the plain sequential pixel-frame.
+// it).  The mode is decided ON THE DEVICE from stage 1's hit fraction (vote::samplesSpeculate): when more than a
+// quarter of the pixels hit, stage 2 exits at once and stage 3 evaluates every sample on demand — the plain sequential
+// pixel-frame — or, under AUTO (PassParams::specGate), leaves the pass to the persistent kernel launched behind it.
 // Exactness: F(k) runs the same operations on the same operands as the sequential loop would at that RNG state, and
 // the additions happen in sample order.
 #pragma once
@@ -83,13 +84,7 @@ RT_DEV Record loadRecord(const PassParams& P, unsigned int j) {
     return r;
 }
 
-// Speculative mode is used when at most half of the owned pixels were queued (sky is visible: paths are short).
-RT_DEV bool specMode(const PassParams& P, unsigned int queued) {
-    if (queued > P.specCapacity) return false;
-    if (P.tune[2] == 1) return true;
-    if (P.tune[2] == 2) return false;
-    return 2ull * queued <= (unsigned long long)P.ownedW * (unsigned long long)P.ownedH && queued <= P.specCapacity;
-}
+RT_DEV bool specMode(const PassParams& P, unsigned int queued) { return vote::samplesSpeculate(P, queued); }
 
 // Round 0's table entries per pixel: the launch's size, clamped so that the queued pixels fit the buffer.
 RT_DEV unsigned int roundK(const PassParams& P, unsigned int pixelsThisRound) {
@@ -346,7 +341,7 @@ __global__ void __launch_bounds__(kThreads) rtSpecChainKernel(const __grid_const
     const unsigned int queued = *P.queueCount;
     const int round = P.specRound;
     const bool speculative = specMode(P, queued);
-    if (round > 0 && !speculative) return;
+    if (!speculative && (round > 0 || P.specGate != 0)) return;   // gated: the persistent kernel renders this pass
     __shared__ ClassTable T;
     buildClassTable(P, round, queued, speculative, T);
     const unsigned int pixelsThisRound = T.pixBase[kClasses];

@@ -103,6 +103,7 @@ struct PassParams {
     uint32_t* chainK;               // parked chain position per queued pixel
     float4* chainColor;             // parked colour sum (xyz) and sample index (w)
     int32_t specRound;
+    int32_t specGate;               // AUTO: samples variant with the persistent kernel as its other branch (see vote::samplesSpeculate)
     int32_t tune[4];                // scheduling thresholds (0 = built-in default); bench tooling only
     int32_t topCount;               // persistent variant: nodes [0, topCount) are staged in shared memory
 };

@@ -152,12 +152,24 @@ RT_DEV f3 lerpDirPre(f3 diffuse, float k0, f3 s1) {
 #define RT_VOTE_SHADE_LANES 12
 #endif
 
+// The samples variant's device-side decision (rt_spec.cuh), made from what stage 1 queued: speculate when few pixels hit
+// the scene (sky is visible: paths are short and most F(k) are used) and the table has room.  tune[2] forces it on / off.
+// With PassParams::specGate the same launch sequence carries BOTH branches — the rounds of rt_spec.cuh, which return at
+// once when the answer is no, and this file's kernel over the whole pass, which returns at once when it is yes.
+RT_DEV bool samplesSpeculate(const PassParams& P, unsigned int queued) {
+    if (queued > P.specCapacity) return false;
+    if (P.tune[2] == 1) return true;
+    if (P.tune[2] == 2) return false;
+    return 4ull * queued <= (unsigned long long)P.ownedW * (unsigned long long)P.ownedH;
+}
+
 #ifndef RT_VOTE_MIN_CTAS
 #define RT_VOTE_MIN_CTAS 6
 #endif
 template <bool COUNT, bool IDS>
 __global__ void __launch_bounds__(kThreads, COUNT ? 1 : RT_VOTE_MIN_CTAS) rtVoteKernel(const __grid_constant__ PassParams P) {
     extern __shared__ uint2 smem[];
+    if (P.specGate != 0 && samplesSpeculate(P, *P.queueCount)) return;    // the samples rounds did this pass
     const DeviceScene& sc = P.scene;
     const uint32_t lane = threadIdx.x & 31u;
     uint2* const stack = smem + threadIdx.x;

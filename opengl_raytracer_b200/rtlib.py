@@ -82,6 +82,7 @@ def load_library(path: str | None = None):
         "rt_set_params": (i, [vp, P(RtParams)]),
         "rt_set_variant": (i, [vp, i]),
         "rt_last_pass_launches": (i, [vp]),
+        "rt_last_pass_variant": (i, [vp]),
         "rt_measure_peaks": (i, [vp, P(ctypes.c_double)]),
         "rt_target_create": (i, [vp, i, i]),
         "rt_target_clear": (i, [vp]),
@@ -198,6 +199,12 @@ class Context:
 
     def last_pass_launches(self) -> int:
         return int(self.lib.rt_last_pass_launches(self.handle))
+
+    def last_pass_variant(self) -> str:
+        code = int(self.lib.rt_last_pass_variant(self.handle))
+        if code < 0:
+            self._check(code)
+        return {v: k for k, v in VARIANTS.items()}.get(code, str(code))
 
     def measure_peaks(self) -> dict:
         """Micro-benchmarked ceilings of this GPU: warp issue, L1 data-pipe wavefronts, L2 -> SM bandwidth."""

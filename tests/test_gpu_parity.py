@@ -344,3 +344,24 @@ def test_async_readback_and_upload_overlap_keep_results(ctx, scene_buffers):
     assert bufs[0].numpy().tobytes() == want_big[0].tobytes()
     assert bufs[1].numpy().tobytes() == want_big[1].tobytes()
     assert bufs[2].numpy().tobytes() == want_small.tobytes()
+
+
+@pytest.mark.parametrize("scene,w,h,spp,expect", [
+    ("cfg4_open", 192, 108, 24, "samples"),        # sky behind the mesh: stage 1 queues few pixels -> the rounds render
+    ("rects_box", 96, 54, 16, "persistent"),       # closed room: every primary ray hits -> the persistent kernel renders
+    ("cfg2_box", 96, 54, 16, "persistent"),
+])
+def test_auto_decides_on_the_device(ctx, oracle_mod, scene_buffers, scene, w, h, spp, expect):
+    """AUTO at >= 16 samples per pixel launches the samples rounds AND the persistent kernel; stage 1's count picks the
+    one that runs.  Either way the frame is the oracle's, bit for bit, over two accumulated frames."""
+    tris, boxes, indices, cfg = scene_buffers(scene)
+    params = cfg.scaled(w, h, spp).params()
+    got = _render_gpu(ctx, tris, boxes, indices, params, 2, "auto", flags=rtlib.PASS_PRIMARY_IDS)
+    assert ctx.last_pass_variant() == expect
+    assert ctx.last_pass_launches() == 13
+    ids = ctx.read_primary_ids()
+    acc = None
+    for frame in range(2):
+        acc, ref_ids, _ = oracle_mod.render_pass(tris, boxes, indices, params.replace(frameNumber=frame), prev=acc, want_ids=True)
+    assert np.array_equal(ids, ref_ids)
+    assert got.tobytes() == acc.tobytes(), f"{(got != acc).any(-1).sum()} pixels differ"
