@@ -227,7 +227,7 @@ cudaError_t rtLaunchPersistent(const PassParams& Pin, bool count, bool ids, int 
     PassParams P = Pin;
     if (P.ownedW <= 0 || P.ownedH <= 0) return cudaSuccess;
     const size_t base = vote::smemBytes(P.scene.stackDepth);
-    if (const char* e = getenv("RT_VOTE_TUNE")) sscanf(e, "%d,%d", &P.tune[0], &P.tune[1]);
+    if (const char* e = getenv("RT_VOTE_TUNE")) sscanf(e, "%d,%d,%d", &P.tune[0], &P.tune[1], &P.tune[2]);   // [2]: same forced decision as the samples rounds (specGate)
     const size_t smem = base;
     cudaError_t e = cudaMemsetAsync(P.workCounter, 0, sizeof(unsigned int), stream);
     if (e != cudaSuccess) return e;
