@@ -283,7 +283,8 @@ int rt_create(rt_ctx** out, int device) {
         cudaMalloc(&c->dWork, sizeof(unsigned int)) != cudaSuccess ||
         cudaMalloc(&c->dQueueCount, sizeof(unsigned int)) != cudaSuccess ||
         cudaMalloc(&c->dWorkArr, size_t(rtSpecWorkUints()) * sizeof(unsigned int)) != cudaSuccess || rtSpecInit() != cudaSuccess) {
-        delete c;
+        cudaGetLastError();
+        rt_destroy(c);          // releases whatever was created (every member starts as null)
         return RT_ERR_CUDA;
     }
     c->stream = c->ownStream;
