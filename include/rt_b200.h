@@ -100,6 +100,9 @@ const char* rt_version(void);
 /* Run on a caller-provided CUDA stream (cudaStream_t as void*; e.g. torch's current stream) so the
  * caller's events bracket the kernels.  NULL restores the context's own stream. */
 int rt_set_stream(rt_ctx* ctx, void* cuda_stream);
+/* The stream the context currently launches on (cudaStream_t as void*).  rt_set_stream orders the new stream behind
+ * the work already queued on the old one, so switching back and forth needs no host synchronisation. */
+void* rt_get_stream(rt_ctx* ctx);
 int rt_sync(rt_ctx* ctx);
 
 /* tris: n_tris x 144 B, boxes: n_boxes x 48 B, indices: n_indices x u32 (layouts: scene.py:45-70).
@@ -137,6 +140,16 @@ int rt_render_pass_ex(rt_ctx* ctx, int frameNumber, int tileX, int tileY, int fl
  * SUM of this GPU's frames instead of the running mean — see rt_render_frames_sum). */
 int rt_render_frames(rt_ctx* ctx, int first_frame, int n_frames);
 int rt_render_frames_sum(rt_ctx* ctx, int first_frame, int n_frames, int frame_stride);
+/* The same with flags.  RT_SUM_CONTINUE: the first pass adds to what the current target already holds (a SUM — see
+ * rt_sum_resume) instead of starting a new sum, so a progressive render can be resumed (first_frame > 0, or after a
+ * checkpoint was restored with rt_write_accum_f32).  Sum mode needs the tile given to rt_set_params to cover the whole
+ * target (numTilesX = numTilesY = 1): a masked pixel would keep the other ping-pong target's stale value, which a
+ * later reduce would add; anything else is refused with RT_ERR_INVALID. */
+enum { RT_SUM_DEFAULT = 0, RT_SUM_CONTINUE = 1 };
+int rt_render_frames_sum_ex(rt_ctx* ctx, int first_frame, int n_frames, int frame_stride, int flags);
+/* Turns the current target from the running MEAN of prior_frames frames (what rt_render_frames / rt_finish_sum leave)
+ * back into their SUM (x prior_frames, one fp32 multiply per channel; alpha untouched); prior_frames = 0 clears it. */
+int rt_sum_resume(rt_ctx* ctx, int prior_frames);
 
 /* Read-backs of the current accumulation target (the one the last pass wrote). */
 int rt_read_accum_f32(rt_ctx* ctx, float* dst_rgba);        /* width*height*4 floats */

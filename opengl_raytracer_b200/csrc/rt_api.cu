@@ -35,6 +35,7 @@ cudaError_t rtLaunchToRgba8(const float4* src, uchar4* dst, size_t n, cudaStream
 cudaError_t rtLaunchBandCopy(float4* target, float4* dense, int width, int rows, int tileSizeY, int numTilesY,
                              int tile, int toDense, cudaStream_t stream);
 cudaError_t rtLaunchFinishSum(float4* target, size_t n, float frames, cudaStream_t stream);
+cudaError_t rtLaunchScaleSum(float4* target, size_t n, float frames, cudaStream_t stream);
 cudaError_t rtLaunchBuildRecords(const float4* raw, const uint32_t* triId, uint32_t nSlots, TriRec* tris, ShadeRec* shade,
                                  cudaStream_t stream);
 
@@ -62,6 +63,7 @@ struct rt_ctx {
     int curSet = 0;
     cudaStream_t upStream = nullptr, downStream = nullptr;   // H2D of an upload / D2H of an asynchronous read-back
     cudaEvent_t evRendered = nullptr;                        // main stream -> downStream
+    cudaEvent_t evSwitch = nullptr;                          // old main stream -> new main stream (rt_set_stream)
     cudaEvent_t evDown[2] = {nullptr, nullptr};              // read-back of target[i] finished (awaited before target[i] is written)
     bool downPending[2] = {false, false};
     DeviceScene scene{};
@@ -274,6 +276,7 @@ int rt_create(rt_ctx** out, int device) {
         cudaStreamCreateWithFlags(&c->upStream, cudaStreamNonBlocking) != cudaSuccess ||
         cudaStreamCreateWithFlags(&c->downStream, cudaStreamNonBlocking) != cudaSuccess ||
         cudaEventCreateWithFlags(&c->evRendered, cudaEventDisableTiming) != cudaSuccess ||
+        cudaEventCreateWithFlags(&c->evSwitch, cudaEventDisableTiming) != cudaSuccess ||
         cudaEventCreateWithFlags(&c->evDown[0], cudaEventDisableTiming) != cudaSuccess ||
         cudaEventCreateWithFlags(&c->evDown[1], cudaEventDisableTiming) != cudaSuccess ||
         cudaEventCreateWithFlags(&c->sets[0].lastUse, cudaEventDisableTiming) != cudaSuccess ||
@@ -302,18 +305,28 @@ void rt_destroy(rt_ctx* c) {
     freeScene(c);
     freeTargets(c);
     cudaFree(c->dCounters); cudaFree(c->dWork); cudaFree(c->dQueueCount); cudaFree(c->dWorkArr);
-    for (cudaEvent_t e : {c->ev0, c->ev1, c->evRendered, c->evDown[0], c->evDown[1], c->sets[0].lastUse, c->sets[1].lastUse})
+    for (cudaEvent_t e : {c->ev0, c->ev1, c->evRendered, c->evSwitch, c->evDown[0], c->evDown[1], c->sets[0].lastUse, c->sets[1].lastUse})
         if (e) cudaEventDestroy(e);
     for (cudaStream_t st : {c->ownStream, c->upStream, c->downStream})
         if (st) cudaStreamDestroy(st);
     delete c;
 }
 
+// The new stream is ordered behind everything already queued on the old one (an event recorded there, awaited here), so
+// a caller may move the context between its own stream and, say, torch's current stream at any point without a host
+// synchronisation and without losing the order of the work (distributed.py does that around its collectives).
 int rt_set_stream(rt_ctx* c, void* s) {
     if (!c) return RT_ERR_INVALID;
-    c->stream = s ? static_cast<cudaStream_t>(s) : c->ownStream;
+    cudaStream_t next = s ? static_cast<cudaStream_t>(s) : c->ownStream;
+    if (next == c->stream) return RT_OK;
+    Bind bind(c);
+    RT_CUDA(c, cudaEventRecord(c->evSwitch, c->stream));
+    RT_CUDA(c, cudaStreamWaitEvent(next, c->evSwitch, 0));
+    c->stream = next;
     return RT_OK;
 }
+
+void* rt_get_stream(rt_ctx* c) { return c ? static_cast<void*>(c->stream) : nullptr; }
 
 int rt_sync(rt_ctx* c) {
     if (!c) return RT_ERR_INVALID;
@@ -695,15 +708,39 @@ int rt_render_frames(rt_ctx* c, int firstFrame, int nFrames) {
 // Frame-sharded progressive mode: this context renders frames firstFrame,
 // firstFrame + stride, ... of tile (params.tileX, params.tileY) and keeps their SUM; the owner of the
 // image adds the shares (NCCL reduce) and calls rt_finish_sum.  Masked pixels are left untouched.
-int rt_render_frames_sum(rt_ctx* c, int firstFrame, int nFrames, int stride) {
+int rt_render_frames_sum_ex(rt_ctx* c, int firstFrame, int nFrames, int stride, int flags) {
     if (!c) return RT_ERR_INVALID;
     if (!c->haveParams) return fail(c, RT_ERR_STATE, "rt_render_frames_sum before rt_set_params");
+    if (!c->target[0]) return fail(c, RT_ERR_STATE, "rt_render_frames_sum before rt_target_create");
     if (stride <= 0) return fail(c, RT_ERR_INVALID, "frame stride must be positive");
+    if (flags & ~RT_SUM_CONTINUE) return fail(c, RT_ERR_INVALID, "unknown rt_render_frames_sum_ex flags %d", flags);
+    const rt_params& u = c->params;
+    if (ownedCount(c->width, u.tileSizeX, u.numTilesX, u.tileX) != c->width ||
+        ownedCount(c->height, u.tileSizeY, u.numTilesY, u.tileY) != c->height)
+        return fail(c, RT_ERR_INVALID, "sum mode needs a tile that covers the target (numTilesX = numTilesY = 1): masked "
+                                       "pixels would carry the other target's stale value into the reduce");
     Bind bind(c);
     for (int k = 0; k < nFrames; k++) {
-        const int rc = renderPass(c, firstFrame + k * stride, c->params.tileX, c->params.tileY, RT_PASS_SKIP_MASKED, k == 0 ? 1 : 2);
+        const int mode = (k == 0 && !(flags & RT_SUM_CONTINUE)) ? 1 : 2;
+        const int rc = renderPass(c, firstFrame + k * stride, u.tileX, u.tileY, RT_PASS_SKIP_MASKED, mode);
         if (rc != RT_OK) return rc;
     }
+    return RT_OK;
+}
+
+int rt_render_frames_sum(rt_ctx* c, int firstFrame, int nFrames, int stride) {
+    return rt_render_frames_sum_ex(c, firstFrame, nFrames, stride, RT_SUM_DEFAULT);
+}
+
+int rt_sum_resume(rt_ctx* c, int priorFrames) {
+    if (!c) return RT_ERR_INVALID;
+    if (!c->target[0]) return fail(c, RT_ERR_STATE, "no target");
+    if (priorFrames < 0) return fail(c, RT_ERR_INVALID, "prior_frames must not be negative");
+    Bind bind(c);
+    waitDownloads(c, c->accumIndex);
+    const size_t n = size_t(c->width) * c->height;
+    if (priorFrames == 0) RT_CUDA(c, cudaMemsetAsync(c->target[c->accumIndex], 0, n * sizeof(float4), c->stream));
+    else RT_CUDA(c, rtLaunchScaleSum(c->target[c->accumIndex], n, float(priorFrames), c->stream));
     return RT_OK;
 }
 

@@ -37,6 +37,35 @@ RT_DEV f3 div3(f3 a, float s) { return mk3(__fdiv_rn(a.x, s), __fdiv_rn(a.y, s),
 RT_DEV f3 normalize3(f3 v) { return div3(v, length3(v)); }
 RT_DEV f3 ld3(const float* p) { return mk3(p[0], p[1], p[2]); }
 
+// 32 bytes through the read-only path in ONE instruction (LDG.E.256.CONSTANT, sm_100+).  Not volatile: scene records
+// never change while a pass runs, so the compiler may schedule, hoist or drop the load like any __ldg.
+#ifndef RT_LDG256
+#define RT_LDG256 1
+#endif
+RT_DEV void ld256(const void* p, float4& lo, float4& hi) {
+#if RT_LDG256
+    asm("ld.global.nc.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+        : "=f"(lo.x), "=f"(lo.y), "=f"(lo.z), "=f"(lo.w), "=f"(hi.x), "=f"(hi.y), "=f"(hi.z), "=f"(hi.w)
+        : "l"(p));
+#else
+    lo = __ldg(reinterpret_cast<const float4*>(p));
+    hi = __ldg(reinterpret_cast<const float4*>(p) + 1);
+#endif
+}
+// One NodeRec: the twelve child bounds in q0..q2 (rt_types.h order) and the two child references.
+RT_DEV void loadNode(const NodeRec* node, float4& q0, float4& q1, float4& q2, int2& refs) {
+    float4 q3;
+    ld256(node, q0, q1);
+    ld256(reinterpret_cast<const char*>(node) + 32, q2, q3);
+    refs = make_int2(__float_as_int(q3.x), __float_as_int(q3.y));
+}
+// One TriRec: v0 | eAB | eAC | N in q0..q2 (the padding half-line rides along with q2).
+RT_DEV void loadTri(const TriRec* rec, float4& q0, float4& q1, float4& q2) {
+    float4 pad;
+    ld256(rec, q0, q1);
+    ld256(reinterpret_cast<const char*>(rec) + 32, q2, pad);
+}
+
 // fragment.glsl:206-218.  float(result)/2^32*2-1: the scalings are exact, so one rounding at the -1.
 RT_DEV float randomValue(uint32_t& state) {
     state = state * 747796405u + 2891336453u;
@@ -86,9 +115,8 @@ struct StackRef {
 // (1/det of a tiny det may be inf/NaN — harmless, the predicate is already false).
 RT_DEV bool triangleTest(const TriRec* __restrict__ rec, f3 o, f3 d, float closestT, float& tOut, float& uOut,
                          float& vOut) {
-    const float4 q0 = __ldg(reinterpret_cast<const float4*>(rec));
-    const float4 q1 = __ldg(reinterpret_cast<const float4*>(rec) + 1);
-    const float4 q2 = __ldg(reinterpret_cast<const float4*>(rec) + 2);
+    float4 q0, q1, q2;
+    loadTri(rec, q0, q1, q2);
     const float EPS = 1e-6f;
     const f3 v0 = mk3(q0.x, q0.y, q0.z), eAB = mk3(q0.w, q1.x, q1.y), eAC = mk3(q1.z, q1.w, q2.x);
     const f3 N = mk3(q2.y, q2.z, q2.w);
@@ -142,9 +170,9 @@ RT_DEV RayHit traverse(const DeviceScene& sc, f3 o, f3 d, StackRef st, WorkCount
         if (cur >= 0) {
             if (cur != RT_REF_NONE) {
                 // internal node: slab-test both children (:281-287); an absent child has NaN bounds -> never hit
-                const float4* np = reinterpret_cast<const float4*>(sc.nodes + cur);
-                const float4 q0 = __ldg(np), q1 = __ldg(np + 1), q2 = __ldg(np + 2);
-                const int2 refs = __ldg(reinterpret_cast<const int2*>(np + 3));
+                float4 q0, q1, q2;
+                int2 refs;
+                loadNode(sc.nodes + cur, q0, q1, q2, refs);
                 if (COUNT) wc.internal++;
                 bool hitA, hitB;
                 const float tA = slabTest(o, inv, q0.x, q0.y, q0.z, q0.w, q1.x, q1.y, hitA);

@@ -171,6 +171,17 @@ __global__ void rtFinishSumKernel(float4* __restrict__ target, size_t n, float f
     }
 }
 
+// rt_sum_resume: running mean of `frames` frames -> their sum (one multiply per colour channel, alpha kept).
+__global__ void rtScaleSumKernel(float4* __restrict__ target, size_t n, float frames) {
+    size_t i = size_t(blockIdx.x) * blockDim.x + threadIdx.x;
+    const size_t step = size_t(gridDim.x) * blockDim.x;
+    for (; i < n; i += step) {
+        float4 p = target[i];
+        p.x = __fmul_rn(p.x, frames); p.y = __fmul_rn(p.y, frames); p.z = __fmul_rn(p.z, frames);
+        target[i] = p;
+    }
+}
+
 // rt_scene_upload: one thread per triangle slot builds its TriRec (v0, the two edges and their cross product, exactly
 // the operations of fragment.glsl:112-116 in that order) and ShadeRec from the caller's 144-byte triangle (nine
 // float4: v0p v0n v1p v1n v2p v2n color emc surface; scene.py:13-30).
@@ -190,12 +201,14 @@ __global__ void rtBuildRecordsKernel(const float4* __restrict__ raw, const uint3
         t[0] = make_float4(v0.x, v0.y, v0.z, abx);
         t[1] = make_float4(aby, abz, acx, acy);
         t[2] = make_float4(acz, nx, ny, nz);
+        t[3] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
         float4* s = reinterpret_cast<float4*>(shade + slot);
         s[0] = make_float4(n0.x, n0.y, n0.z, n1.x);
         s[1] = make_float4(n1.y, n1.z, n2.x, n2.y);
         s[2] = make_float4(n2.z, col.x, col.y, col.z);
         s[3] = make_float4(emc.x, emc.y, emc.z, surf.x);
         s[4] = make_float4(surf.y, 0.0f, 0.0f, 0.0f);
+        s[5] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
     }
 }
 
@@ -433,6 +446,11 @@ cudaError_t rtLaunchBandCopy(float4* target, float4* dense, int width, int rows,
 
 cudaError_t rtLaunchFinishSum(float4* target, size_t n, float frames, cudaStream_t stream) {
     rtFinishSumKernel<<<148 * 8, 256, 0, stream>>>(target, n, frames);
+    return cudaGetLastError();
+}
+
+cudaError_t rtLaunchScaleSum(float4* target, size_t n, float frames, cudaStream_t stream) {
+    rtScaleSumKernel<<<148 * 8, 256, 0, stream>>>(target, n, frames);
     return cudaGetLastError();
 }
 

@@ -280,9 +280,9 @@ __global__ void __launch_bounds__(T, 1) rtPoolKernel(const __grid_constant__ Pas
                     if (mode == MODE_DEEP) {
                         bool goNear = false;
                         if (cur != RT_REF_NONE) {
-                            const float4* np = reinterpret_cast<const float4*>(sc.nodes + cur);
-                            const float4 q0 = __ldg(np), q1 = __ldg(np + 1), q2 = __ldg(np + 2);
-                            const int2 refs = __ldg(reinterpret_cast<const int2*>(np + 3));
+                            float4 q0, q1, q2;
+                            int2 refs;
+                            loadNode(sc.nodes + cur, q0, q1, q2, refs);
                             const StepOut r = nodeMath(o, inv, bestT, q0, q1, q2, refs);
                             if (COUNT) { wInternal++; wPops += r.hits; }
                             if (r.pushFar) {

@@ -11,9 +11,11 @@ struct SurfaceHit {
 // fragment.glsl:146-174 for the winning triangle only (deferred: the shader does this per candidate,
 // the inputs of the winner are the same).
 RT_DEV SurfaceHit resolveHit(const DeviceScene& sc, const RayHit& h, f3 o, f3 d) {
-    const float4* sp = reinterpret_cast<const float4*>(sc.shade + h.slot);
-    const float4 s0 = __ldg(sp), s1 = __ldg(sp + 1), s2 = __ldg(sp + 2), s3 = __ldg(sp + 3);
-    const float rough = __ldg(reinterpret_cast<const float*>(sp + 4));
+    const char* sp = reinterpret_cast<const char*>(sc.shade + h.slot);
+    float4 s0, s1, s2, s3;
+    ld256(sp, s0, s1);
+    ld256(sp + 32, s2, s3);
+    const float rough = __ldg(reinterpret_cast<const float*>(sp + 64));
     SurfaceHit r;
     r.point = add3(o, scale3(d, h.t));
     const float w = sub(sub(1.0f, h.u), h.v);

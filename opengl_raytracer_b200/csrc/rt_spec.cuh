@@ -38,9 +38,27 @@ constexpr int kJumpLo = 256, kJumpHi = 64;   // offsets k < kJumpLo * kJumpHi ca
 constexpr int kMaxK = kJumpLo * kJumpHi;
 __constant__ uint2 cJumpLo[kJumpLo];         // (a, c) of 3k draws, k < 256: state' = a * state + c
 __constant__ uint2 cJumpHi[kJumpHi];         // (a, c) of 3 * 256 * h draws
+// h blocks of 3 * 256 draws applied to state s by square-and-multiply, `block` = the (a, c) of one block: affine maps
+// of one LCG commute, so any order of composition is the same map.  Only for offsets beyond the tables.
+__host__ __device__ inline uint32_t jumpBlocks(uint32_t s, unsigned int h, uint2 block) {
+    uint32_t ba = block.x, bc = block.y;
+    for (; h != 0u; h >>= 1) {
+        if (h & 1u) s = s * ba + bc;
+        bc = ba * bc + bc;
+        ba = ba * ba;
+    }
+    return s;
+}
 RT_DEV uint32_t jumpSeed(uint32_t seed, unsigned int k) {
-    const uint2 lo = cJumpLo[k & (kJumpLo - 1)], hi = cJumpHi[k >> 8];
-    return (seed * lo.x + lo.y) * hi.x + hi.y;
+    const uint2 lo = cJumpLo[k & (kJumpLo - 1)];
+    const uint32_t s = seed * lo.x + lo.y;
+    const unsigned int h = k >> 8;
+    if (h < (unsigned int)kJumpHi) {
+        const uint2 hi = cJumpHi[h];
+        return s * hi.x + hi.y;
+    }
+    // k >= kMaxK (rays_per_pixel x hits >= 16384: thousands of samples in a closed room): no table entry, compose
+    return jumpBlocks(s, h, cJumpHi[1]);
 }
 
 // Table sizes.  Round 0 gives every queued pixel rays_per_pixel samples at up to 1.25 hits each (open-sky chains run

@@ -4,14 +4,18 @@
 // triangleIndices[] u32.  rt_scene_upload re-lays them out, bit-preservingly, so the
 // traversal touches only what it needs, with 16-byte vector loads through the read-only path:
 //
+// Records are 32-byte aligned and fetched with 256-bit loads (ld.global.nc.v8.f32 = LDG.E.256, sm_100+): the L1 data pipe
+// charges a divergent load one wavefront per 128-byte line per INSTRUCTION whatever its width, so a 64-byte node costs
+// two wavefronts per lane instead of four (profiles/r02_ldg256.md: 200 G vs 120 G records/s L1-resident).
+//
 //   NodeRec  64 B  one per REACHABLE internal node: the bounds of BOTH children (the shader slab-tests
 //                  both children when it expands a node, fragment.glsl:285-287) + two child references.
 //                  A popped node's own bounds are never re-fetched: its tNear travels with the stack
 //                  entry (the re-test at fragment.glsl:261 recomputes the same value from the same inputs).
-//   TriRec   48 B  one per triangle slot, in leaf order (removes the triangleIndices indirection):
-//                  v0, eAB = v1-v0, eAC = v2-v0, N = cross(eAB,eAC), all computed on the host with the
-//                  shader's operation order and no contraction (fragment.glsl:112-116).
-//   ShadeRec 80 B  one per triangle slot: the three vertex normals + material, fetched once per ray for
+//   TriRec   64 B  one per triangle slot, in leaf order (removes the triangleIndices indirection):
+//                  v0, eAB = v1-v0, eAC = v2-v0, N = cross(eAB,eAC) (48 B + padding to two 32-byte halves), computed at
+//                  upload with the shader's operation order and no contraction (fragment.glsl:112-116).
+//   ShadeRec 96 B  one per triangle slot: the three vertex normals + material, fetched once per ray for
 //                  the winning triangle only (the shader copies them for every candidate, :151-173).
 //   triId    4 B   per slot: the original triangle index (primary-id image only).
 //
@@ -29,26 +33,28 @@
 #define RT_MAX_SLOTS (1u << (31 - RT_LEAF_BITS))
 #define RT_MAX_STACK 64
 
-struct alignas(16) NodeRec {
+struct alignas(32) NodeRec {
     float aMinX, aMinY, aMinZ, aMaxX;
     float aMaxY, aMaxZ, bMinX, bMinY;
     float bMinZ, bMaxX, bMaxY, bMaxZ;
     int32_t refA, refB, pad0, pad1;
 };
 
-struct alignas(16) TriRec {
+struct alignas(32) TriRec {
     float v0x, v0y, v0z, abx;
     float aby, abz, acx, acy;
     float acz, nx, ny, nz;
+    float pad[4];
 };
 
-struct alignas(16) ShadeRec {
+struct alignas(32) ShadeRec {
     float n0x, n0y, n0z, n1x;
     float n1y, n1z, n2x, n2y;
     float n2z, colR, colG, colB;
     float emcR, emcG, emcB, emission;
-    float roughness, pad0, pad1, pad2;
+    float roughness, pad[7];
 };
+static_assert(sizeof(NodeRec) == 64 && sizeof(TriRec) == 64 && sizeof(ShadeRec) == 96, "record sizes");
 
 struct DeviceScene {
     const NodeRec* nodes;

@@ -91,9 +91,9 @@ template <bool COUNT>
 RT_DEV void stepInternal(const DeviceScene& sc, Lane& L, uint2* stack, uint32_t stride, uint32_t* cnt) {
     bool goNear = false;
     if (L.cur != RT_REF_NONE) {
-        const float4* np = reinterpret_cast<const float4*>(sc.nodes + L.cur);
-        const float4 q0 = __ldg(np), q1 = __ldg(np + 1), q2 = __ldg(np + 2);
-        const int2 refs = __ldg(reinterpret_cast<const int2*>(np + 3));
+        float4 q0, q1, q2;
+        int2 refs;
+        loadNode(sc.nodes + L.cur, q0, q1, q2, refs);
         bool hitA, hitB;
         const float tA = slabTest(L.o, L.inv, q0.x, q0.y, q0.z, q0.w, q1.x, q1.y, hitA);
         const float tB = slabTest(L.o, L.inv, q1.z, q1.w, q2.x, q2.y, q2.z, q2.w, hitB);

@@ -15,10 +15,32 @@ The path shards two ways, both taken from the reference's own mechanisms:
 Samples inside one pixel-frame are never split: the RNG state is carried across them (fragment.glsl:358-363).
 The functions take the renderer as an object with the rtlib.Context methods they call, so the CPU tests can
 drive the same logic with gloo and a stand-in renderer.
+
+Stream order: the renderer's kernels (pass, band pack / unpack, sum, finish) and torch's collectives must run in
+program order.  ``render_tile_mode`` and ``render_frame_mode`` therefore move the context onto torch's current stream for
+their duration (``rt_set_stream`` orders the new stream behind the work already queued on the old one, both ways) and
+put it back afterwards — the caller needs no ``use_torch_stream()`` or ``sync()`` of its own.
 """
 from __future__ import annotations
 
+import contextlib
+
 import numpy as np
+
+
+@contextlib.contextmanager
+def on_torch_stream(ctx):
+    """Run ``ctx`` on torch's current CUDA stream inside the block (no-op for a renderer without streams, e.g. the
+    CPU tests' stand-in), so collectives issued through torch.distributed order with the renderer's kernels."""
+    switch = getattr(ctx, "use_torch_stream", None)
+    if switch is None:
+        yield
+        return
+    previous = switch()
+    try:
+        yield
+    finally:
+        ctx.set_stream(previous)
 
 
 def band_params(params, rank: int, world: int, band_rows: int = 8):
@@ -59,31 +81,43 @@ def render_tile_mode(ctx, dist, params, rank: int, world: int, frame: int = 0, b
     import torch
     p = band_params(params, rank, world, band_rows)
     ctx.set_params(p)
-    ctx.render_pass(frame, 0, rank, flags=4)                    # RT_PASS_SKIP_MASKED
     if world == 1:
+        ctx.render_pass(frame, 0, rank, flags=4)                # RT_PASS_SKIP_MASKED
         return dense
-    rows = max_band_rows(params.height, band_rows, world)
-    if dense is None:
-        dense = torch.empty((rows, params.width, 4), dtype=torch.float32, device="cuda")
-    ctx.band_gather(rank, dense.data_ptr())
-    bufs = gather_bands(dist, dense, rank, world)
-    if rank == 0:
-        for g in range(1, world):
-            ctx.band_scatter(g, bufs[g].data_ptr())
+    with on_torch_stream(ctx):
+        ctx.render_pass(frame, 0, rank, flags=4)
+        rows = max_band_rows(params.height, band_rows, world)
+        if dense is None:
+            dense = torch.empty((rows, params.width, 4), dtype=torch.float32, device=getattr(ctx, "torch_device", "cuda"))
+        ctx.band_gather(rank, dense.data_ptr())
+        bufs = gather_bands(dist, dense, rank, world)
+        if rank == 0:
+            for g in range(1, world):
+                ctx.band_scatter(g, bufs[g].data_ptr())
     return dense
 
 
 def render_frame_mode(ctx, dist, params, rank: int, world: int, first_frame: int, n_frames: int, accum_tensor):
     """Progressive accumulation sharded by frames.  ``accum_tensor(ctx)`` returns a torch view of the current
-    target; after the reduce rank 0's target holds the mean of all frames."""
+    target; after the reduce rank 0's target holds the mean of frames 0 .. first_frame + n_frames - 1.
+
+    ``first_frame > 0`` continues a render: rank 0's current target must hold the running mean of frames
+    0 .. first_frame - 1 (left by an earlier call, by ``render_frames``, or restored from a checkpoint); it is turned
+    back into a sum (``rt_sum_resume``) that rank 0's new frames are added to, the other ranks start from zero, and the
+    final division is by ``first_frame + n_frames``.  ``params`` must describe the whole frame (numTilesX = numTilesY =
+    1): ``rt_render_frames_sum`` refuses partial tiles."""
     first, count, stride = frame_share(first_frame, n_frames, rank, world)
     ctx.set_params(params)
-    if count:
-        ctx.render_frames_sum(first, count, stride)
-    view = accum_tensor(ctx)
-    if count == 0:
-        view.zero_()
-    if world > 1:
-        dist.reduce(view, dst=0)
-    if rank == 0:
-        ctx.finish_sum(n_frames)
+    with on_torch_stream(ctx):
+        resume = rank == 0 and first_frame > 0
+        if resume:
+            ctx.sum_resume(first_frame)
+        if count:
+            ctx.render_frames_sum(first, count, stride, resume=resume)
+        view = accum_tensor(ctx)
+        if count == 0 and not resume:
+            view.zero_()
+        if world > 1:
+            dist.reduce(view, dst=0)
+        if rank == 0:
+            ctx.finish_sum(first_frame + n_frames)

@@ -55,6 +55,7 @@ class RtParams(ctypes.Structure):
 COUNTER_NAMES = ("rays", "rays_traced", "internal", "leaves", "tri_tests", "hits", "pops", "paths")
 VARIANTS = {"auto": 0, "pixel": 1, "persistent": 2, "wavefront": 3, "pool": 4, "samples": 5}
 PASS_COUNTERS, PASS_PRIMARY_IDS, PASS_SKIP_MASKED = 1, 2, 4
+SUM_CONTINUE = 1
 
 _lib = None
 
@@ -76,6 +77,7 @@ def load_library(path: str | None = None):
         "rt_last_error": (ctypes.c_char_p, [vp]),
         "rt_version": (ctypes.c_char_p, []),
         "rt_set_stream": (i, [vp, vp]),
+        "rt_get_stream": (vp, [vp]),
         "rt_sync": (i, [vp]),
         "rt_scene_upload": (i, [vp, vp, u32, vp, u32, vp, u32]),
         "rt_scene_free": (i, [vp]),
@@ -91,6 +93,8 @@ def load_library(path: str | None = None):
         "rt_render_pass_ex": (i, [vp, i, i, i, i]),
         "rt_render_frames": (i, [vp, i, i]),
         "rt_render_frames_sum": (i, [vp, i, i, i]),
+        "rt_render_frames_sum_ex": (i, [vp, i, i, i, i]),
+        "rt_sum_resume": (i, [vp, i]),
         "rt_read_accum_f32": (i, [vp, vp]),
         "rt_write_accum_f32": (i, [vp, vp]),
         "rt_read_accum_f32_async": (i, [vp, vp]),
@@ -213,7 +217,12 @@ class Context:
         return {"issue_gwarpinst_s": out[0], "l1_gwavefronts_s": out[1], "l2_gbs": out[2]}
 
     def set_stream(self, cuda_stream: int | None):
+        """Launch on ``cuda_stream`` (a cudaStream_t as int; None = the context's own stream).  The new stream is
+        ordered behind the work already queued on the old one, so switching needs no host synchronisation."""
         self._check(self.lib.rt_set_stream(self.handle, ctypes.c_void_p(cuda_stream or 0)))
+
+    def get_stream(self) -> int:
+        return int(self.lib.rt_get_stream(self.handle) or 0)
 
     def sync(self):
         self._check(self.lib.rt_sync(self.handle))
@@ -237,8 +246,14 @@ class Context:
     def render_frames(self, first_frame: int, n_frames: int):
         self._check(self.lib.rt_render_frames(self.handle, first_frame, n_frames))
 
-    def render_frames_sum(self, first_frame: int, n_frames: int, frame_stride: int = 1):
-        self._check(self.lib.rt_render_frames_sum(self.handle, first_frame, n_frames, frame_stride))
+    def render_frames_sum(self, first_frame: int, n_frames: int, frame_stride: int = 1, resume: bool = False):
+        """Frames first, first + stride, ... kept as a SUM in the targets.  ``resume``: add to what the current target
+        holds (see :meth:`sum_resume`) instead of starting a new sum."""
+        self._check(self.lib.rt_render_frames_sum_ex(self.handle, first_frame, n_frames, frame_stride, SUM_CONTINUE if resume else 0))
+
+    def sum_resume(self, prior_frames: int):
+        """Current target: running mean of ``prior_frames`` frames -> their sum (0 clears it)."""
+        self._check(self.lib.rt_sum_resume(self.handle, prior_frames))
 
     def finish_sum(self, total_frames: int):
         self._check(self.lib.rt_finish_sum(self.handle, total_frames))
@@ -316,13 +331,20 @@ class Context:
         self._check(self.lib.rt_timer_stop(self.handle, ctypes.byref(ms)))
         return ms.value
 
-    def use_torch_stream(self):
-        """Run on torch's current CUDA stream so torch events and NCCL collectives order with the kernels."""
+    @property
+    def torch_device(self) -> str:
+        return f"cuda:{self.device}"
+
+    def use_torch_stream(self) -> int:
+        """Run on torch's current CUDA stream so torch events and NCCL collectives order with the kernels.  Returns the
+        stream the context was on (hand it to :meth:`set_stream` to go back; the switch keeps the order both ways)."""
         import torch
-        handle = torch.cuda.current_stream().cuda_stream
+        previous = self.get_stream()
+        handle = torch.cuda.current_stream(self.device).cuda_stream
         # torch reports the legacy default stream as 0, which rt_set_stream reads as "back to the context's own
         # stream"; cudaStreamLegacy (0x1) is the explicit handle of that stream
         self.set_stream(handle if handle else 1)
+        return previous
 
     def accum_tensor(self, which: int = -1):
         """Zero-copy torch view (H, W, 4) float32 of an accumulation target (optional tensor hand-off)."""

@@ -23,6 +23,20 @@ int main() {
             checked++;
         }
     }
+    // offsets beyond the tables (k >= kMaxK) go through jumpBlocks: compare with stepping, incl. the table boundary
+    for (uint32_t seed : seeds) {
+        uint32_t s = seed;
+        const unsigned int last = 3u * (unsigned int)spec::kMaxK + 77u;
+        for (unsigned int k = 0; k <= last; k++) {
+            if (k >= (unsigned int)spec::kMaxK - 2u && (k < (unsigned int)spec::kMaxK + 600u || k % 97u == 0u || k == last)) {
+                const uint2 a = lo[k & (spec::kJumpLo - 1)];
+                const uint32_t jumped = spec::jumpBlocks(seed * a.x + a.y, k >> 8, hi[1]);
+                if (jumped != s) { std::printf("far jump mismatch seed %u k %u: %u vs %u\n", seed, k, jumped, s); return 1; }
+                checked++;
+            }
+            s = stepLcg(stepLcg(stepLcg(s)));
+        }
+    }
     unsigned int prev = 0;
     for (int c = 0; c < spec::kClasses; c++) {
         const unsigned int K = spec::classK(c);

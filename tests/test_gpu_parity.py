@@ -365,3 +365,110 @@ def test_auto_decides_on_the_device(ctx, oracle_mod, scene_buffers, scene, w, h,
         acc, ref_ids, _ = oracle_mod.render_pass(tris, boxes, indices, params.replace(frameNumber=frame), prev=acc, want_ids=True)
     assert np.array_equal(ids, ref_ids)
     assert got.tobytes() == acc.tobytes(), f"{(got != acc).any(-1).sum()} pixels differ"
+
+
+class _OneDeviceDist:
+    """torch.distributed stand-in that plays a W-rank job on ONE device, rank after rank: `gather` / `reduce` are
+    torch ops on torch's CURRENT stream (as NCCL's are ordered with it), so the renderer's kernels and the 'collective'
+    only see each other's results if distributed.py orders the two streams — there is no host synchronisation here."""
+
+    def __init__(self, world):
+        self.world, self.dense, self.sums = world, {}, []
+        self.rank = 0
+
+    def gather(self, tensor, gather_list=None, dst=0):
+        if self.rank != dst:
+            self.dense[self.rank] = tensor.clone()
+            return
+        for g in range(self.world):
+            gather_list[g].copy_(tensor if g == dst else self.dense[g])
+
+    def reduce(self, tensor, dst=0):
+        if self.rank != dst:
+            self.sums.append(tensor.clone())
+            return
+        for other in self.sums:
+            tensor.add_(other)
+
+
+def test_distributed_functions_order_their_own_streams(ctx, scene_buffers):
+    """render_tile_mode / render_frame_mode on a context that keeps ITS OWN stream while torch's current
+    stream is a side stream: the functions themselves order renderer kernels and collectives (rt_set_stream keeps the
+    order across the switch), no use_torch_stream() / sync() by the caller.  Tile mode reassembles bit-exactly, frame
+    mode (run in two instalments: first_frame > 0 continues the mean) matches the sequential running mean."""
+    import torch
+    from opengl_raytracer_b200 import distributed
+    tris, boxes, indices, cfg = scene_buffers("rects_box")
+    w, h, world = 640, 360, 3
+    params = cfg.scaled(w, h, 2).params()
+    full = _render_gpu(ctx, tris, boxes, indices, params, 1, "auto")
+    mean7 = _render_gpu(ctx, tris, boxes, indices, cfg.scaled(w, h, 1).params(), 7, "auto")
+    ctx.set_stream(None)
+    own = ctx.get_stream()
+    side = torch.cuda.Stream()
+    fake = _OneDeviceDist(world)
+    with torch.cuda.stream(side):
+        for rank in list(range(1, world)) + [0]:            # rank 0 last: it needs the others' bands
+            fake.rank = rank
+            ctx.target_clear()
+            distributed.render_tile_mode(ctx, fake, params, rank, world, frame=0, band_rows=8)
+            assert ctx.get_stream() == own                   # put back where it was
+        assert ctx.read_accum_f32().tobytes() == full.tobytes()
+        # frame mode, frames 0..2 then 3..6 continued; every 'rank' uses the one context, so rank 0's mean is kept aside
+        p1 = cfg.scaled(w, h, 1).params()
+        kept = None
+        for first, n in ((0, 3), (3, 4)):
+            fake.sums = []
+            for rank in list(range(1, world)) + [0]:
+                fake.rank = rank
+                ctx.target_clear()
+                if rank == 0 and kept is not None:
+                    previous = ctx.use_torch_stream()        # (scaffolding: the copy is a torch op on the side stream)
+                    ctx.accum_tensor().copy_(kept)
+                    ctx.set_stream(previous)
+                distributed.render_frame_mode(ctx, fake, p1, rank, world, first, n, lambda c: c.accum_tensor())
+            kept = ctx.accum_tensor().clone()
+    got = ctx.read_accum_f32()
+    assert np.abs(got[..., :3] - mean7[..., :3]).max() < 2e-5 and (got[..., 3] == 1).all()
+
+
+def test_sum_mode_continuation_and_partial_tiles(ctx, scene_buffers):
+    """rt_render_frames_sum_ex(RT_SUM_CONTINUE) adds to the sum the target holds; rt_sum_resume turns a mean back
+    into a sum; a tile that does not cover the target is refused (masked pixels would carry stale values)."""
+    tris, boxes, indices, cfg = scene_buffers("rects_box")
+    params = cfg.scaled(80, 45, 1).params()
+    _render_gpu(ctx, tris, boxes, indices, params, 0, "pixel")
+    ctx.target_clear()
+    ctx.render_frames_sum(0, 5, 1)
+    whole = ctx.read_accum_f32()
+    ctx.target_clear()
+    ctx.render_frames_sum(0, 2, 1)
+    ctx.render_frames_sum(2, 3, 1, resume=True)
+    assert ctx.read_accum_f32().tobytes() == whole.tobytes()
+    # mean of 2 frames -> sum -> 3 more frames -> mean of 5
+    ctx.target_clear()
+    ctx.render_frames(0, 2)
+    ctx.sum_resume(2)
+    ctx.render_frames_sum(2, 3, 1, resume=True)
+    ctx.finish_sum(5)
+    a = ctx.read_accum_f32()
+    ctx.target_clear()
+    ctx.render_frames(0, 5)
+    assert np.abs(a[..., :3] - ctx.read_accum_f32()[..., :3]).max() < 1e-5
+    ctx.set_params(params.replace(tileSizeY=8, numTilesY=2))
+    with pytest.raises(RuntimeError, match="covers the target"):
+        ctx.render_frames_sum(0, 1, 1)
+    ctx.set_params(params)
+
+
+@pytest.mark.parametrize("mode", ["0,0,1"], ids=["speculative"])
+def test_samples_offsets_beyond_the_jump_tables(ctx, oracle_mod, scene_buffers, monkeypatch, mode):
+    """rays_per_pixel x hits beyond kMaxK = 16384 (closed room, 11 bounces, 2100 samples): the chain's RNG
+    offsets leave the jump tables and are composed instead; still bit-exact."""
+    monkeypatch.setenv("RT_VOTE_TUNE", mode)
+    tris, boxes, indices, cfg = scene_buffers("rects_box")
+    params = cfg.scaled(6, 4, 2100).params(bounces=10)
+    got = _render_gpu(ctx, tris, boxes, indices, params, 1, "samples")
+    acc, _, cnt = oracle_mod.render_pass(tris, boxes, indices, params, want_counters=True)
+    assert cnt["hits"] // (6 * 4) > 16384                     # the offsets really do leave the tables
+    assert got.tobytes() == acc.tobytes(), f"{(got != acc).any(-1).sum()} pixels differ"
