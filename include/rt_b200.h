@@ -79,8 +79,12 @@ enum {
     RT_VARIANT_SAMPLES = 5,     /* primary stage -> the samples of each hit pixel evaluated in parallel (LCG jump-ahead,
                                    speculative start offsets) -> per-pixel chain; falls back to sequential samples on the
                                    device when most primary rays hit */
-    RT_VARIANT_POOL = 4         /* persistent CTAs, K rays per lane pooled in shared memory, extend / leaf / shade
+    RT_VARIANT_POOL = 4,        /* persistent CTAs, K rays per lane pooled in shared memory, extend / leaf / shade
                                    stages picked by warp vote, top of the tree staged in shared memory */
+    RT_VARIANT_CHAIN = 6        /* primary stage -> ONE persistent kernel in which each warp evaluates the samples of a few
+                                   hit pixels in parallel (as SAMPLES does) and resolves their sample chains in shared memory
+                                   while the evaluations run; the persistent kernel renders the pass instead when the
+                                   device-side gate finds that most primary rays hit */
 };
 
 /* flags for rt_render_pass_ex */

@@ -25,6 +25,8 @@ cudaError_t rtLaunchPersistent(const PassParams& P, bool count, bool ids, int sm
 cudaError_t rtLaunchPool(const PassParams& P, bool count, bool ids, int sms, cudaStream_t stream);
 cudaError_t rtLaunchWavefront(const PassParams& P, bool count, bool ids, int sms, cudaStream_t stream);
 cudaError_t rtLaunchSamples(const PassParams& P, bool ids, int sms, uint32_t* todoA, uint32_t* todoB, cudaStream_t stream);
+cudaError_t rtLaunchChain(const PassParams& P, bool ids, int sms, cudaStream_t stream);
+size_t rtChainRingBytes(int sms);
 cudaError_t rtMeasurePeaks(int sms, cudaStream_t stream, double* out);
 int rtSpecRounds();
 int rtSpecLaunches();
@@ -92,7 +94,7 @@ struct rt_ctx {
     float4* dQueueD = nullptr;
     float4* dQueueE = nullptr;
     float4* dSpecBuf = nullptr;
-    size_t specRecords = 0, specBufEntries = 0;
+    size_t specRecords = 0, specBufEntries = 0, recPlanes = 0;
     unsigned int* dWorkArr = nullptr;     // work counters of the rounds + todo counts
     uint32_t* dTodo[2] = {nullptr, nullptr};
     uint32_t* dChainClass = nullptr;
@@ -103,6 +105,7 @@ struct rt_ctx {
     uint32_t lastCapacity = 0;
     uint32_t* dChainK = nullptr;
     float4* dChainColor = nullptr;
+    float4* dChainRing = nullptr;         // chain variant: rings of the helped pixel slots (allocated on first use)
 };
 
 namespace {
@@ -175,29 +178,40 @@ void freeQueue(rt_ctx* c) {
     c->dTodo[0] = c->dTodo[1] = nullptr; c->dChainK = nullptr; c->dChainColor = nullptr; c->dChainClass = nullptr;
     c->dQueueA = c->dQueueB = nullptr; c->dQueuePix = nullptr; c->dQueueWork = nullptr;
     c->dQueueC = c->dQueueD = c->dQueueE = c->dSpecBuf = nullptr;
-    c->queueCapacity = 0; c->specRecords = 0; c->specBufEntries = 0;
+    c->queueCapacity = 0; c->specRecords = 0; c->specBufEntries = 0; c->recPlanes = 0;
 }
 
 cudaError_t ensureQueue(rt_ctx* c, bool withWork);
 
+// Samples and chain variants: the five record planes of the queue (80 bytes per pixel of the target).
+cudaError_t ensureRecordPlanes(rt_ctx* c) {
+    cudaError_t e = ensureQueue(c, false);
+    if (e != cudaSuccess) return e;
+    if (c->recPlanes < c->queueCapacity) {
+        cudaFree(c->dQueueC); cudaFree(c->dQueueD); cudaFree(c->dQueueE);
+        c->dQueueC = c->dQueueD = c->dQueueE = nullptr; c->recPlanes = 0;
+        if ((e = cudaMalloc(&c->dQueueC, c->queueCapacity * sizeof(float4))) != cudaSuccess) return e;
+        if ((e = cudaMalloc(&c->dQueueD, c->queueCapacity * sizeof(float4))) != cudaSuccess) return e;
+        if ((e = cudaMalloc(&c->dQueueE, c->queueCapacity * sizeof(float4))) != cudaSuccess) return e;
+        c->recPlanes = c->queueCapacity;
+    }
+    return cudaSuccess;
+}
+
 // Samples variant: record planes for every pixel of the target, and a table of K entries for up to half of the
 // pixels this pass owns (the speculative mode is only entered when at most half of them were queued).
 cudaError_t ensureSpec(rt_ctx* c, size_t ownedPixels, int K, uint32_t* capacityOut) {
-    cudaError_t e = ensureQueue(c, false);
+    cudaError_t e = ensureRecordPlanes(c);
     if (e != cudaSuccess) return e;
     if (c->specRecords < c->queueCapacity) {
-        cudaFree(c->dQueueC); cudaFree(c->dQueueD); cudaFree(c->dQueueE);
         cudaFree(c->dTodo[0]); cudaFree(c->dTodo[1]); cudaFree(c->dChainK); cudaFree(c->dChainColor); cudaFree(c->dChainClass);
-        c->dQueueC = c->dQueueD = c->dQueueE = nullptr; c->specRecords = 0;
+        c->specRecords = 0;
         c->dTodo[0] = c->dTodo[1] = nullptr; c->dChainK = nullptr; c->dChainColor = nullptr; c->dChainClass = nullptr;
         if ((e = cudaMalloc(&c->dTodo[0], c->queueCapacity * sizeof(uint32_t))) != cudaSuccess) return e;
         if ((e = cudaMalloc(&c->dTodo[1], c->queueCapacity * sizeof(uint32_t))) != cudaSuccess) return e;
         if ((e = cudaMalloc(&c->dChainK, c->queueCapacity * sizeof(uint32_t))) != cudaSuccess) return e;
         if ((e = cudaMalloc(&c->dChainClass, c->queueCapacity * sizeof(uint32_t))) != cudaSuccess) return e;
         if ((e = cudaMalloc(&c->dChainColor, c->queueCapacity * sizeof(float4))) != cudaSuccess) return e;
-        if ((e = cudaMalloc(&c->dQueueC, c->queueCapacity * sizeof(float4))) != cudaSuccess) return e;
-        if ((e = cudaMalloc(&c->dQueueD, c->queueCapacity * sizeof(float4))) != cudaSuccess) return e;
-        if ((e = cudaMalloc(&c->dQueueE, c->queueCapacity * sizeof(float4))) != cudaSuccess) return e;
         c->specRecords = c->queueCapacity;
     }
     // (test tooling: RT_VOTE_TUNE=..,..,1 forces the speculative mode, which then needs room for every pixel)
@@ -304,7 +318,7 @@ void rt_destroy(rt_ctx* c) {
     if (c->downStream) cudaStreamSynchronize(c->downStream);
     freeScene(c);
     freeTargets(c);
-    cudaFree(c->dCounters); cudaFree(c->dWork); cudaFree(c->dQueueCount); cudaFree(c->dWorkArr);
+    cudaFree(c->dCounters); cudaFree(c->dWork); cudaFree(c->dQueueCount); cudaFree(c->dWorkArr); cudaFree(c->dChainRing);
     for (cudaEvent_t e : {c->ev0, c->ev1, c->evRendered, c->evSwitch, c->evDown[0], c->evDown[1], c->sets[0].lastUse, c->sets[1].lastUse})
         if (e) cudaEventDestroy(e);
     for (cudaStream_t st : {c->ownStream, c->upStream, c->downStream})
@@ -535,7 +549,7 @@ int rt_set_params(rt_ctx* c, const rt_params* p) {
 
 int rt_set_variant(rt_ctx* c, int variant) {
     if (!c) return RT_ERR_INVALID;
-    if (variant < RT_VARIANT_AUTO || variant > RT_VARIANT_SAMPLES) return fail(c, RT_ERR_INVALID, "unknown variant %d", variant);
+    if (variant < RT_VARIANT_AUTO || variant > RT_VARIANT_CHAIN) return fail(c, RT_ERR_INVALID, "unknown variant %d", variant);
     c->variant = variant;
     return RT_OK;
 }
@@ -621,29 +635,47 @@ int renderPass(rt_ctx* c, int frameNumber, int tileX, int tileY, int flags, int 
     }
     cudaError_t e;
     int variant = c->variant;
-    // AUTO, by measurement on B200 (profiles/r01_variants.md).  Fewer than 8 samples per pixel: the one-thread-per-pixel
-    // kernel.  More make the per-pixel work uneven (sky pixels finish at once, surface pixels run rays_per_pixel paths):
-    // the persistent warp-vote kernel.  When this GPU's share of the frame is small (a tile-sharded frame on several
-    // GPUs, or a small frame) the serial sample chain of a pixel bounds the pass, and where the sky is visible the samples
-    // variant, which evaluates the samples in parallel, wins (dragon 4K 64 spp, share 1 / 1/2 / 1/4 / 1/8: persistent
-    // 27.3 / 16.5 / 14.0 / 12.5 ms, samples 31.9 / 16.4 / 8.9 / 4.8 ms) — but in a closed room, or where many pixels
-    // hit, it loses (1080p 16 spp: 18.5 vs 10.4 ms open, 145 vs 121 ms boxed).  Which case it is only the primary rays
-    // tell, so the pass is launched with BOTH branches and stage 1's count decides on the device (specGate).
+    // AUTO, by measurement on B200 (profiles/r01_variants.md, r02_variants.md).  Fewer than 8 samples per pixel: the
+    // one-thread-per-pixel kernel.  More make the per-pixel work uneven (sky pixels finish at once, surface pixels run
+    // rays_per_pixel paths): the persistent warp-vote kernel.  From 16 samples per pixel the serial sample chain of a pixel
+    // (the RNG state is carried from sample to sample) starts to bound the pass — its tail on a whole frame, all of it on a
+    // tile-sharded frame's 1/N share — and where the sky is visible the two variants that evaluate samples ahead of the
+    // chain win: CHAIN (a pixel per lane, idle lanes help their neighbours' chains; no table, little waste) for a large
+    // share, SAMPLES (every offset of every hit pixel through a table, in rounds) for a small one (dragon 4K 64 spp, share
+    // 1 / 1/2 / 1/4 / 1/8: persistent 27.2 / 16.5 / 14.0 / 12.3 ms, chain 26.2 / 16.2 / 13.0 / 10.6, samples 30.3 / 16.4 /
+    // 8.9 / 4.6).  In a closed room, or where most pixels hit, both lose to the persistent kernel (box 4K 8 spp: chain 162
+    // vs 155 ms).  Which case it is only the primary rays tell, so the pass is launched with BOTH branches and stage 1's
+    // count of hit pixels decides on the device (specGate).
     bool gated = false;
+    const bool canSpeculate = P.counters == nullptr && c->width <= 65535 && c->height <= 65535;   // no counting instantiation; px | py << 16
     if (variant == RT_VARIANT_AUTO) {
         const long long owned = (long long)P.ownedW * P.ownedH, manyPixels = (long long)c->smCount * 2048 * 16;
         variant = u.rays_per_pixel < 8 ? RT_VARIANT_PIXEL : RT_VARIANT_PERSISTENT;
-        if (u.rays_per_pixel >= 16 && owned <= manyPixels && P.counters == nullptr && c->width <= 65535 && c->height <= 65535 &&
-            sumMode == 0) {
-            variant = RT_VARIANT_SAMPLES;
+        if (u.rays_per_pixel >= 16 && canSpeculate && sumMode == 0) {
+            variant = owned <= manyPixels ? RT_VARIANT_SAMPLES : RT_VARIANT_CHAIN;
             gated = true;
         }
     }
-    // the samples variant evaluates paths the reference would not (speculation): it has no counting instantiation
-    if (variant == RT_VARIANT_SAMPLES && (P.counters != nullptr || c->width > 65535 || c->height > 65535))
-        variant = RT_VARIANT_PERSISTENT;
+    // the speculative variants evaluate paths the reference would not: they have no counting instantiation
+    if ((variant == RT_VARIANT_SAMPLES || variant == RT_VARIANT_CHAIN) && !canSpeculate) variant = RT_VARIANT_PERSISTENT;
     if (variant == RT_VARIANT_WAVEFRONT && (c->width > 65535 || c->height > 65535)) variant = RT_VARIANT_PIXEL;
-    if (variant == RT_VARIANT_SAMPLES) {
+    if (variant == RT_VARIANT_CHAIN && (u.nBounces > 63 || (long long)u.rays_per_pixel * std::max(u.nBounces, 1) >= (1ll << 25)))
+        variant = RT_VARIANT_PERSISTENT;       // the chain variant's ring tags hold hits < 64 and offsets < 2^26
+    if (variant == RT_VARIANT_CHAIN) {
+        e = ensureRecordPlanes(c);
+        if (e != cudaSuccess) return fail(c, RT_ERR_NOMEM, "chain queue: %s", cudaGetErrorString(e));
+        P.queueA = c->dQueueA; P.queueB = c->dQueueB; P.queueC = c->dQueueC; P.queueD = c->dQueueD; P.queueE = c->dQueueE;
+        P.queueCount = c->dQueueCount; P.workCounters = c->dWorkArr;
+        if (!c->dChainRing && cudaMalloc(&c->dChainRing, rtChainRingBytes(c->smCount)) != cudaSuccess) {
+            cudaGetLastError();
+            return fail(c, RT_ERR_NOMEM, "chain rings: %zu bytes", rtChainRingBytes(c->smCount));
+        }
+        P.chainRing = c->dChainRing;
+        P.specCapacity = 0xffffffffu;          // no table to fit: the gate is the hit fraction alone
+        P.specGate = gated ? 1 : 0;            // AUTO: the persistent kernel is the other branch; forced: the chain kernel alone
+        e = rtLaunchChain(P, P.primaryIds != nullptr, c->smCount, c->stream);
+        if (e == cudaSuccess && gated) e = rtLaunchPersistent(P, false, P.primaryIds != nullptr, c->smCount, c->stream);
+    } else if (variant == RT_VARIANT_SAMPLES) {
         const int K = rtSpecTableK(u.rays_per_pixel, u.nBounces);
         uint32_t capacity = 0;
         e = ensureSpec(c, size_t(P.ownedW) * size_t(P.ownedH), K, &capacity);
@@ -669,7 +701,8 @@ int renderPass(rt_ctx* c, int frameNumber, int tileX, int tileY, int flags, int 
     else
         e = rtLaunchPixel(P, P.counters != nullptr, P.primaryIds != nullptr, c->stream);
     if (e != cudaSuccess) return fail(c, RT_ERR_CUDA, "kernel launch: %s", cudaGetErrorString(e));
-    c->lastLaunches = variant == RT_VARIANT_SAMPLES ? rtSpecLaunches() + (gated ? 1 : 0) : variant == RT_VARIANT_WAVEFRONT ? 2 : 1;
+    c->lastLaunches = variant == RT_VARIANT_SAMPLES ? rtSpecLaunches() + (gated ? 1 : 0) : variant == RT_VARIANT_CHAIN ? (gated ? 3 : 2)
+                      : variant == RT_VARIANT_WAVEFRONT ? 2 : 1;
     c->lastVariant = variant; c->lastGated = gated;
     c->lastOwned = (long long)P.ownedW * P.ownedH; c->lastCapacity = P.specCapacity;
     cudaEventRecord(c->sets[c->curSet].lastUse, c->stream);     // the next upload into this set waits for it
@@ -799,7 +832,7 @@ int rt_last_pass_variant(rt_ctx* c) {
     int forced = 0, t0 = 0, t1 = 0;
     if (const char* v = getenv("RT_VOTE_TUNE")) sscanf(v, "%d,%d,%d", &t0, &t1, &forced);
     const bool speculate = queued <= c->lastCapacity && (forced == 1 || (forced != 2 && 4ll * queued <= c->lastOwned));
-    return speculate ? RT_VARIANT_SAMPLES : RT_VARIANT_PERSISTENT;
+    return speculate ? c->lastVariant : RT_VARIANT_PERSISTENT;
 }
 
 int rt_measure_peaks(rt_ctx* c, double* out3) {

@@ -17,6 +17,7 @@
 #include "rt_pool.cuh"
 #include "rt_wave.cuh"
 #include "rt_spec.cuh"
+#include "rt_chain.cuh"
 
 namespace {
 
@@ -216,6 +217,7 @@ __global__ void rtBuildRecordsKernel(const float4* __restrict__ raw, const uint3
 
 // ------------------------------------------------------------------------------------- launchers
 // (C++ linkage, called from rt_api.cu)
+int rtChainMaxBlocksPerSm();
 size_t rtPixelKernelSmem(int stackDepth) { return size_t(stackDepth) * kBlockThreads * sizeof(uint2); }
 
 cudaError_t rtLaunchPixel(const PassParams& P, bool count, bool ids, cudaStream_t stream) {
@@ -430,6 +432,64 @@ cudaError_t rtLaunchSamples(const PassParams& Pin, bool ids, int sms, uint32_t* 
         if (!tables) break;
     }
     return cudaSuccess;
+}
+
+// ---- CHAIN variant: primary stage -> queue -> ONE persistent kernel (a pixel per lane + in-warp sample stealing)
+int rtChainMaxBlocksPerSm() { return 8; }
+size_t rtChainRingBytes(int sms) { return chain::ringBytes(sms * rtChainMaxBlocksPerSm()); }
+
+cudaError_t rtLaunchChain(const PassParams& Pin, bool ids, int sms, cudaStream_t stream) {
+    PassParams P = Pin;
+    if (P.ownedW <= 0 || P.ownedH <= 0) return cudaSuccess;
+    if (const char* e = getenv("RT_VOTE_TUNE")) sscanf(e, "%d,%d,%d,%d", &P.tune[0], &P.tune[1], &P.tune[2], &P.tune[3]);
+    P.chainTune[0] = 16; P.chainTune[1] = 1; P.chainTune[2] = chain::kRing; P.chainTune[3] = 0;   // quota scale (sixteenths), helping, window, scattered queue order (off: see r02_variants.md)
+    if (const char* e = getenv("RT_CHAIN_TUNE")) sscanf(e, "%d,%d,%d,%d", &P.chainTune[0], &P.chainTune[1], &P.chainTune[2], &P.chainTune[3]);
+    cudaError_t e = cudaMemsetAsync(P.workCounters, 0, 64 * sizeof(unsigned int), stream);
+    if (e != cudaSuccess) return e;
+    if ((e = cudaMemsetAsync(P.queueCount, 0, sizeof(unsigned int), stream)) != cudaSuccess) return e;
+    const size_t smem = spec::smemBytes(P.scene.stackDepth);
+    dim3 grid((P.ownedW + 15) / 16, (P.ownedH + 7) / 8);
+    if (smem > 48 * 1024) {
+        cudaFuncSetAttribute(spec::rtSpecPrimaryKernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem));
+        cudaFuncSetAttribute(spec::rtSpecPrimaryKernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem));
+    }
+#ifdef RT_CHAIN_STATS
+    struct StatsPrinter {
+        const PassParams& P; cudaStream_t stream;
+        ~StatsPrinter() {
+            unsigned long long v[8]; unsigned int q = 0;
+            cudaStreamSynchronize(stream);
+            cudaMemcpy(v, P.workCounters + 16, sizeof v, cudaMemcpyDeviceToHost);
+            cudaMemcpy(&q, P.queueCount, sizeof q, cudaMemcpyDeviceToHost);
+            fprintf(stderr, "chain stats: queued %u  started %llu own %llu busy-iters %llu dropped %llu rays %llu idle-iters %llu shade-sections(lanes) %llu used %llu\n",
+                    q, v[0], v[1], v[2], v[3], v[4], v[5], v[6], v[7]);
+            unsigned long long x[12];
+            cudaMemcpy(x, P.workCounters + 32, sizeof x, cudaMemcpyDeviceToHost);
+            fprintf(stderr, "   warp iterations max %llu sum %llu; warp life max %.3f ms, sum %.1f ms; lives in 2 ms bins:", x[0], x[1], x[2] * 1e-6, x[3] * 1e-6);
+            for (int i = 0; i < 8; i++) fprintf(stderr, " %llu", x[4 + i]);
+            fprintf(stderr, "\n");
+        }
+    } printer{P, stream};
+#endif
+    if (ids) spec::rtSpecPrimaryKernel<true><<<grid, spec::kThreads, smem, stream>>>(P);
+    else spec::rtSpecPrimaryKernel<false><<<grid, spec::kThreads, smem, stream>>>(P);
+    if ((e = cudaGetLastError()) != cudaSuccess) return e;
+    if (P.nBounces <= 1 || P.raysPerPixel <= 0) return cudaSuccess;   // nothing was queued
+    const size_t smemChain = chain::smemBytes(P.scene.stackDepth);
+    if (smemChain > 48 * 1024) {
+        e = cudaFuncSetAttribute(chain::rtChainKernel, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smemChain));
+        if (e != cudaSuccess) return e;
+    }
+    int perSm = 0;
+    if ((e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSm, chain::rtChainKernel, chain::kThreads, smemChain)) != cudaSuccess) return e;
+    if (perSm < 1) perSm = 1;
+    if (const char* v = getenv("RT_VOTE_CTAS")) perSm = std::max(1, std::min(perSm, atoi(v)));
+    perSm = std::min(perSm, rtChainMaxBlocksPerSm());      // what rt_api.cu sized the rings for
+    const long long pixels = (long long)P.ownedW * P.ownedH;
+    const long long want = (pixels + chain::kThreads - 1) / chain::kThreads;
+    const int gridChain = int(std::min<long long>((long long)sms * perSm, std::max<long long>(want, 1)));
+    chain::rtChainKernel<<<gridChain, chain::kThreads, smemChain, stream>>>(P);
+    return cudaGetLastError();
 }
 
 cudaError_t rtLaunchToRgba8(const float4* src, uchar4* dst, size_t n, cudaStream_t stream) {

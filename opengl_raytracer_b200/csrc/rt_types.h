@@ -112,4 +112,6 @@ struct PassParams {
     int32_t specGate;               // AUTO: samples variant with the persistent kernel as its other branch (see vote::samplesSpeculate)
     int32_t tune[4];                // scheduling thresholds (0 = built-in default); bench tooling only
     int32_t topCount;               // persistent variant: nodes [0, topCount) are staged in shared memory
+    int32_t chainTune[4];           // chain variant: quota scale (sixteenths), helping on/off, window, scattered queue order
+    float4* chainRing;              // chain variant: kRing entries per lane of the grid (global memory)
 };

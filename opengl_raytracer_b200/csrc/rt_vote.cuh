@@ -30,10 +30,13 @@ namespace vote {
 #define RT_VOTE_THREADS 128
 #endif
 constexpr int kThreads = RT_VOTE_THREADS;
-constexpr int kBurst = 4;
+#ifndef RT_VOTE_BURST
+#define RT_VOTE_BURST 4
+#endif
+constexpr int kBurst = RT_VOTE_BURST;
 // per lane: normal0 (3), k0, s1 (3), origin0 (3), incoming0 (3), rayColor0 (3), stop0
 constexpr int kScratchWords = 17;
-constexpr int MODE_INTERNAL = 0, MODE_LEAF = 1, MODE_SHADE = 2, MODE_DONE = 3;
+constexpr int MODE_INTERNAL = 0, MODE_LEAF = 1, MODE_SHADE = 2, MODE_DONE = 3, MODE_HIT = 4;
 
 inline size_t smemBytes(int stackDepth) {
     return size_t(stackDepth) * kThreads * sizeof(uint2) + size_t(kScratchWords) * kThreads * sizeof(uint32_t);

@@ -53,7 +53,7 @@ class RtParams(ctypes.Structure):
 
 
 COUNTER_NAMES = ("rays", "rays_traced", "internal", "leaves", "tri_tests", "hits", "pops", "paths")
-VARIANTS = {"auto": 0, "pixel": 1, "persistent": 2, "wavefront": 3, "pool": 4, "samples": 5}
+VARIANTS = {"auto": 0, "pixel": 1, "persistent": 2, "wavefront": 3, "pool": 4, "samples": 5, "chain": 6}
 PASS_COUNTERS, PASS_PRIMARY_IDS, PASS_SKIP_MASKED = 1, 2, 4
 SUM_CONTINUE = 1
 

@@ -25,6 +25,10 @@ def test_reference_arm_prints_one_contract_line():
     assert d["cpu_baseline"]["value"] == d["value"] and "64 spp" in d["cpu_baseline"]["sample"]
     assert d["e2e"] == {"value": d["value"], "unit": "Mrays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}
     assert "cfg4_open" in d["config"]["workload"]
+    # the driver compares the two arms' `config` objects: both come from one function
+    sys.path.insert(0, ROOT)
+    import bench
+    assert d["config"] == bench.bench_config(1) and set(d["config"]) == {"workload", "parallelism", "l2", "ray_unit"}
 
 
 class _RecordingContext:

@@ -9,7 +9,7 @@ from opengl_raytracer_b200 import rtlib
 
 pytestmark = pytest.mark.gpu
 
-VARIANTS = ["pixel", "persistent", "pool", "wavefront", "samples"]
+VARIANTS = ["pixel", "persistent", "pool", "wavefront", "samples", "chain"]
 EXACT_COUNTERS = ("rays", "internal", "leaves", "tri_tests", "hits", "pops", "paths")
 
 
@@ -87,13 +87,15 @@ def test_image_ids_counters_match_oracle(ctx, oracle_mod, scene_buffers, scene, 
     ("rects_box", 40, 24, 40, 1, {"bounces": 7}),         # 8 hits per sample: the last round's bound, a full table buffer
     ("cfg2_box", 64, 36, 48, 2, {}),
 ])
-def test_samples_variant_matches_oracle(ctx, oracle_mod, scene_buffers, monkeypatch, scene, w, h, spp, frames, over, mode):
-    """The samples variant (parallel evaluation of F(k) + per-pixel chain) without counting flags, in its device-chosen
-    mode and with either mode forced: RGBA32F bit-exact against the oracle, primary ids exact."""
+@pytest.mark.parametrize("variant", ["samples", "chain"])
+def test_samples_variant_matches_oracle(ctx, oracle_mod, scene_buffers, monkeypatch, scene, w, h, spp, frames, over, mode, variant):
+    """The speculative variants (parallel evaluation of F(k) + per-pixel chain; SAMPLES through a global table in rounds,
+    CHAIN inside one warp) without counting flags, in their device-chosen mode and with either mode forced: RGBA32F
+    bit-exact against the oracle, primary ids exact."""
     monkeypatch.setenv("RT_VOTE_TUNE", mode)
     tris, boxes, indices, cfg = scene_buffers(scene)
     params = cfg.scaled(w, h, spp).params(**over)
-    got = _render_gpu(ctx, tris, boxes, indices, params, frames, "samples", flags=rtlib.PASS_PRIMARY_IDS)
+    got = _render_gpu(ctx, tris, boxes, indices, params, frames, variant, flags=rtlib.PASS_PRIMARY_IDS)
     ids = ctx.read_primary_ids()
     acc = None
     for frame in range(frames):
@@ -245,6 +247,26 @@ def test_full_size_band_against_oracle(ctx, oracle_mod, scene_buffers):
     want, _, _ = oracle_mod.render_pass(tris, boxes, indices, band)
     rows = slice(17 * 16, 18 * 16)
     assert got[rows].tobytes() == want[rows].tobytes()
+
+
+def test_full_size_auto_runs_the_chain_variant(ctx, oracle_mod, scene_buffers):
+    """The bench workload's shape (dragon under open sky, 3840x2160, here 16 spp): AUTO carries the chain variant and the
+    persistent kernel, stage 1's count picks the chain variant on the device; the frame equals the persistent kernel's
+    bit for bit, and an oracle spot-check of one 8-row band of it is bit-exact.  In the closed room the same launch
+    sequence leaves the pass to the persistent kernel."""
+    tris, boxes, indices, cfg = scene_buffers("cfg4_open")
+    params = cfg.scaled(3840, 2160, 16).params()
+    a = _render_gpu(ctx, tris, boxes, indices, params, 1, "auto")
+    assert ctx.last_pass_variant() == "chain" and ctx.last_pass_launches() == 3
+    b = _render_gpu(ctx, tris, boxes, indices, params, 1, "persistent")
+    assert a.tobytes() == b.tobytes()
+    band = params.replace(tileSizeX=3840, numTilesX=1, tileSizeY=8, numTilesY=270, tileY=140)
+    want, _, _ = oracle_mod.render_pass(tris, boxes, indices, band)
+    rows = slice(140 * 8, 141 * 8)
+    assert a[rows].tobytes() == want[rows].tobytes()
+    tris, boxes, indices, cfg = scene_buffers("cfg4_box")
+    _render_gpu(ctx, tris, boxes, indices, cfg.scaled(3840, 2160, 16).params(), 1, "auto")
+    assert ctx.last_pass_variant() == "persistent"
 
 
 def test_headless_app_loop_and_checkpoint(tmp_path, oracle_mod):
@@ -461,14 +483,15 @@ def test_sum_mode_continuation_and_partial_tiles(ctx, scene_buffers):
     ctx.set_params(params)
 
 
+@pytest.mark.parametrize("variant", ["samples", "chain"])
 @pytest.mark.parametrize("mode", ["0,0,1"], ids=["speculative"])
-def test_samples_offsets_beyond_the_jump_tables(ctx, oracle_mod, scene_buffers, monkeypatch, mode):
+def test_samples_offsets_beyond_the_jump_tables(ctx, oracle_mod, scene_buffers, monkeypatch, mode, variant):
     """rays_per_pixel x hits beyond kMaxK = 16384 (closed room, 11 bounces, 2100 samples): the chain's RNG
     offsets leave the jump tables and are composed instead; still bit-exact."""
     monkeypatch.setenv("RT_VOTE_TUNE", mode)
     tris, boxes, indices, cfg = scene_buffers("rects_box")
     params = cfg.scaled(6, 4, 2100).params(bounces=10)
-    got = _render_gpu(ctx, tris, boxes, indices, params, 1, "samples")
+    got = _render_gpu(ctx, tris, boxes, indices, params, 1, variant)
     acc, _, cnt = oracle_mod.render_pass(tris, boxes, indices, params, want_counters=True)
     assert cnt["hits"] // (6 * 4) > 16384                     # the offsets really do leave the tables
     assert got.tobytes() == acc.tobytes(), f"{(got != acc).any(-1).sum()} pixels differ"

@@ -1,0 +1,12 @@
+#!/bin/bash
+set -u
+mkdir -p gpurun_out
+timeout 600 python -m pytest tests/test_gpu_parity.py -x -q -k "chain" > gpurun_out/r2i_pytest.log 2>&1; echo "pytest rc=$?"; tail -3 gpurun_out/r2i_pytest.log
+for B in 1 2 4 8; do python tools/prof_case.py cfg4_open 3840 2160 64 chain 3 $B; done
+for Q in 12 8 6; do RT_CHAIN_TUNE=$Q,1,32,1 python tools/prof_case.py cfg4_open 3840 2160 64 chain 3 8; done
+RT_CHAIN_TUNE=8,1,32,1 python tools/prof_case.py cfg4_open 3840 2160 64 chain 3 4
+RT_CHAIN_TUNE=8,1,32,1 python tools/prof_case.py cfg4_open 3840 2160 64 chain 3 1
+RT_CHAIN_TUNE=16,1,32,0 python tools/prof_case.py cfg4_open 3840 2160 64 chain 3 1
+export RT_B200_LIB=$PWD/opengl_raytracer_b200/csrc/librt_b200_stats.so
+python tools/prof_case.py cfg4_open 3840 2160 64 chain 2 8 2>&1
+RT_CHAIN_TUNE=8,1,32,1 python tools/prof_case.py cfg4_open 3840 2160 64 chain 2 8 2>&1

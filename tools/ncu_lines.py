@@ -1,12 +1,13 @@
 """Join ncu's per-instruction SASS metrics (--page source --csv) with nvdisasm line info, aggregate per source line.
-usage: python tools/ncu_lines.py <report.ncu-rep> <mangled-kernel-name-substring> [top_n] [--outer] [--cubin rt_kernels]
+usage: python tools/ncu_lines.py <report.ncu-rep> <mangled-kernel-name-substring> [top_n] [--outer] [--cubin rt_kernels] [--filter kernel-regex]
        [--sections name:first-last,name:first-last,...]
 Default: the innermost inlined frame of each instruction (which arithmetic helper).  --outer: the outermost frame (the
 line of the kernel's own file that the instruction was inlined into: which part of the kernel); with --sections the
 outer lines are summed over named line ranges.  Needs the same librt_b200.so that was profiled."""
 import csv, io, os, re, subprocess, sys, tempfile, collections
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
-args = [a for a in sys.argv[1:] if not a.startswith("--")]
+skip = {sys.argv[i + 1] for i, a in enumerate(sys.argv[:-1]) if a in ("--cubin", "--sections", "--filter")}
+args = [a for a in sys.argv[1:] if not a.startswith("--") and a not in skip]
 rep, kern = args[0], args[1]
 topn = int(args[2]) if len(args) > 2 else 45
 outer = "--outer" in sys.argv
@@ -41,7 +42,8 @@ for l in dis[start + 1:]:
             last = group[-1] if outer else group[0]
         fresh = False
         lines.append(last)
-out = subprocess.run(["ncu", "-i", rep, "--page", "source", "--csv"], capture_output=True, text=True).stdout
+flt = ["-k", "regex:" + sys.argv[sys.argv.index("--filter") + 1]] if "--filter" in sys.argv else []   # reports with several kernels
+out = subprocess.run(["ncu", "-i", rep, "--page", "source", "--csv"] + flt, capture_output=True, text=True).stdout
 rows = list(csv.reader(io.StringIO(out)))
 h = next(i for i, r in enumerate(rows) if r and r[0] == "Address")
 hdr = rows[h]
