@@ -49,7 +49,8 @@ def bench_config(world):
     cfg = configs.scene_configs()[WORKLOAD]
     return {"workload": f"{WORKLOAD}: models/dragon (37,986 triangles) under open sky, {cfg.width}x{cfg.height}, "
                         f"{cfg.rays_per_pixel} spp, {cfg.bounces} bounces, 1 frame",
-            "parallelism": f"b200 arm: tile mode, {world} x interleaved {BAND_ROWS}-row bands, NCCL gather to rank 0; "
+            "parallelism": f"b200 arm: tile mode, {world} x interleaved {BAND_ROWS}-row bands, assembled on rank 0 (the render "
+                           "kernels store their pixels into rank 0's target over NVLink; 4-byte all-reduces as fences); "
                            "reference arm: rank 0's host cores",
             "l2": "b200 arm: 256 MiB memset between steps, inside the timed region; reference arm: a bounded sample of the "
                   "frame per step (cpu_baseline.sample)",
@@ -249,12 +250,18 @@ def run_gpu(args):
         ctx.set_params(params)
         ctx.target_create(cfg.width, cfg.height)
         dense = None
+        # exchange step of tile mode: peer stores from inside the render kernels (default), or pack / NCCL gather / unpack
+        peer = None
+        if world > 1 and args.exchange == "peer":
+            peer = distributed.open_peer_targets(ctx, dist, rank, world)
+            if peer is None and rank == 0:
+                sys.stderr.write("bench: peer mapping refused, falling back to the NCCL gather exchange\n")
 
         def step(frame=0, clear=True):
             nonlocal dense
             if clear:
                 ctx.target_clear()
-            dense = distributed.render_tile_mode(ctx, dist, params, rank, world, frame, BAND_ROWS, dense)
+            dense = distributed.render_tile_mode(ctx, dist, params, rank, world, frame, BAND_ROWS, dense, peer=peer)
 
         # work counters of one step (untimed; reference-equivalent counts, rays_traced = actual traversals)
         ctx.reset_counters()
@@ -290,6 +297,17 @@ def run_gpu(args):
             flush_buf.zero_()                                   # L2 flush between steps (inside the timed region)
             ctx.target_clear()
             ctx.set_params(distributed.band_params(params, rank, world, BAND_ROWS))
+            if peer is not None:
+                if rank == 0:
+                    ctx.target_wait_reads()
+                dist.all_reduce(peer.token)                     # fence: rank 0 has cleared the target the peers write
+                ev[1].record()
+                ctx.render_pass(0, 0, rank, flags=rtlib.PASS_SKIP_MASKED | (rtlib.PASS_TO_PEER if rank else 0))
+                ev[2].record()
+                dist.all_reduce(peer.token)                     # fence: every rank's kernels and their stores are done
+                ev[3].record()
+                kernel_events.append(ev[:4])
+                return
             ev[1].record()
             ctx.render_pass(0, 0, rank, flags=rtlib.PASS_SKIP_MASKED)
             ev[2].record()
@@ -328,7 +346,10 @@ def run_gpu(args):
         if os.environ.get("RT_BENCH_TRACE"):
             for ev in kernel_events:
                 sys.stderr.write(f"rank {rank} step phases ms: " + " ".join(f"{a.elapsed_time(b):.3f}" for a, b in zip(ev, ev[1:])) + "\n")
-        if world > 1:
+        if peer is not None:
+            # phase 0 includes the fence before the pass, "fence_after" the wait for the slowest rank; rank 0's view
+            phases.update({"pass_max_over_ranks": max_over_ranks(kernel_ms), "fence_after": phase(2)})
+        elif world > 1:
             # where a multi-GPU step goes: slowest rank's pass, then pack / NCCL gather (includes waiting for the
             # slowest rank) / scatter; rank 0's view
             phases.update({"pass_max_over_ranks": max_over_ranks(kernel_ms), "pack": phase(2), "nccl_gather": phase(3),
@@ -338,7 +359,8 @@ def run_gpu(args):
                "mrays_s": total["rays_traced"] / (ms_step * 1e-3) / 1e6,
                "ref_equiv_mrays_s": total["rays"] / (ms_step * 1e-3) / 1e6, "clocks": clocks,
                "local_alg_bytes": local_alg_bytes, "launches": steps, "phases_ms": phases,
-               "pass_launches": ctx.last_pass_launches(), "variant": ctx.last_pass_variant()}   # traversal-kernel passes; the caller multiplies by kernels per pass
+               "pass_launches": ctx.last_pass_launches(), "variant": ctx.last_pass_variant(),
+               "exchange": "none" if world == 1 else "peer" if peer is not None else "gather"}   # traversal-kernel passes; the caller multiplies by kernels per pass
         if with_e2e:
             # end to end through the C ABI with HOST buffers: every step uploads the scene (H2D from pinned memory),
             # sets the uniforms, draws, gathers, and reads the RGBA32F frame back on rank 0 (D2H into pinned memory).
@@ -375,6 +397,9 @@ def run_gpu(args):
                           "note": "copies overlap the neighbouring steps' render (second scene-buffer set + upload "
                                   "stream, asynchronous read-back); serial_ms_per_step = blocking read-back every step"}
             res["e2e_launches"] = steps
+        if peer is not None:
+            peer.close()            # before rank 0 re-creates (frees) the targets the others have mapped
+            barrier()
         res["scene"] = (tris, boxes, indices)
         return res
 
@@ -450,7 +475,8 @@ def run_gpu(args):
             # this repo's kernels launched by rank 0 inside the timed region: the pass (1 kernel; the samples variant
             # launches its primary stage + rounds of sort/evaluate/chain kernels: the library reports the count) + band
             # gather (1) and scatters (N - 1)
-            "gpu_launches": main["launches"] * (main["pass_launches"] + (world if world > 1 else 0))}
+            "exchange": main["exchange"],
+            "gpu_launches": main["launches"] * (main["pass_launches"] + (world if main["exchange"] == "gather" else 0))}
 
     if world == 1 and not args.no_cpu:
         line["cpu_baseline"] = cpu_baseline(args)
@@ -501,6 +527,8 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--variant", default="auto", choices=["auto", "pixel", "persistent", "wavefront", "pool", "samples", "chain"])
+    ap.add_argument("--exchange", default="peer", choices=["peer", "gather"],
+                    help="N > 1: how the bands reach rank 0 (peer = stores from inside the render kernels over NVLink)")
     ap.add_argument("--spp", type=int, default=0, help="override samples per pixel (not a valid bench number)")
     ap.add_argument("--no-box", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")

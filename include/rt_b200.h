@@ -72,7 +72,8 @@ enum {
 
 /* Kernel variants (rt_set_variant); all produce identical results. */
 enum {
-    RT_VARIANT_AUTO = 0,
+    RT_VARIANT_AUTO = 0,        /* by measurement: PIXEL below 8 samples per pixel, else PERSISTENT; from 16 samples per pixel
+                                   CHAIN (large share of a frame) or SAMPLES (small share) if the gate finds open sky */
     RT_VARIANT_PIXEL = 1,       /* one thread per pixel, whole pixel-frame in one kernel */
     RT_VARIANT_PERSISTENT = 2,  /* persistent warps fetching pixels with warp-aggregated atomics */
     RT_VARIANT_WAVEFRONT = 3,   /* generate / extend / shade kernels over compacted ray queues */
@@ -81,10 +82,11 @@ enum {
                                    device when most primary rays hit */
     RT_VARIANT_POOL = 4,        /* persistent CTAs, K rays per lane pooled in shared memory, extend / leaf / shade
                                    stages picked by warp vote, top of the tree staged in shared memory */
-    RT_VARIANT_CHAIN = 6        /* primary stage -> ONE persistent kernel in which each warp evaluates the samples of a few
-                                   hit pixels in parallel (as SAMPLES does) and resolves their sample chains in shared memory
-                                   while the evaluations run; the persistent kernel renders the pass instead when the
-                                   device-side gate finds that most primary rays hit */
+    RT_VARIANT_CHAIN = 6        /* primary stage -> ONE persistent kernel, a hit pixel per lane running its sample chain in
+                                   order; lanes without a pixel (the tail of a frame, or a small share of one) evaluate a
+                                   neighbour's next samples ahead of its chain and hand the results over through a small
+                                   ring; the persistent kernel renders the pass instead when the device-side gate finds
+                                   that most primary rays hit */
 };
 
 /* flags for rt_render_pass_ex */
@@ -92,8 +94,10 @@ enum {
     RT_PASS_DEFAULT = 0,
     RT_PASS_COUNTERS = 1,      /* accumulate the work counters (slower kernel instantiation) */
     RT_PASS_PRIMARY_IDS = 2,   /* record the primary-hit triangle id image (-1 = miss) */
-    RT_PASS_SKIP_MASKED = 4    /* pixels outside the tile are left untouched instead of copied from
+    RT_PASS_SKIP_MASKED = 4,   /* pixels outside the tile are left untouched instead of copied from
                                   the previous target (multi-GPU band sharding: each GPU owns its rows) */
+    RT_PASS_TO_PEER = 8        /* also store every owned pixel into the peer targets opened with rt_peer_open
+                                  (peer tile mode, below) */
 };
 
 int rt_create(rt_ctx** out, int device);
@@ -180,6 +184,27 @@ int rt_set_accum_index(rt_ctx* ctx, int index);
 int rt_band_rows(rt_ctx* ctx, int tileY);                                   /* how many rows */
 int rt_band_gather(rt_ctx* ctx, int tileY, void* dense_dev);                /* target -> dense */
 int rt_band_scatter(rt_ctx* ctx, int tileY, const void* dense_dev);         /* dense -> target */
+
+/* Peer tile mode: the exchange step of tile mode folded into the render kernels.  The assembling rank exports its two
+ * targets (CUDA IPC; same node, NVLink / NVSwitch peers), every other rank maps them and renders its bands with
+ * RT_PASS_TO_PEER: each finished pixel is stored into its own target AND, over NVLink, into the assembling rank's
+ * (posted 16-byte stores, issued as pixels finish, so the transfer overlaps the tracing and nothing is packed,
+ * gathered or unpacked afterwards).  It replaces the reference's single framebuffer that all tiles of a frame are
+ * drawn into (main.py:376-401 with the tile mask of fragment.glsl:382).
+ *   Contract: all ranks have targets of the same size and flip them in lockstep (same sequence of passes /
+ * rt_target_clear; rt_accum_index must agree), because a pass writes target[1 - rt_accum_index] on both sides.
+ * The caller fences across ranks BEFORE a peer pass (the assembling rank has finished clearing / reading the target
+ * about to be written: rt_target_wait_reads, then any collective) and AFTER it (peers' kernels have completed
+ * before the assembling rank reads the frame); opengl_raytracer_b200/distributed.py does both with a 4-byte
+ * all-reduce.  rt_peer_close (or rt_destroy) unmaps; close the peers before the exporter re-creates its target. */
+#define RT_IPC_HANDLE_BYTES 64
+int rt_peer_export(rt_ctx* ctx, void* handles_out);      /* 2 * RT_IPC_HANDLE_BYTES: target 0, target 1 */
+int rt_peer_open(rt_ctx* ctx, const void* handles);      /* 2 * RT_IPC_HANDLE_BYTES from the exporter  */
+int rt_peer_close(rt_ctx* ctx);
+int rt_peer_is_open(rt_ctx* ctx);
+/* Order the stream behind any asynchronous read-back of the target the next pass will write. */
+int rt_target_wait_reads(rt_ctx* ctx);
+
 /* sum target -> mean RGBA32F in place: target = target * (1 / n_frames) is NOT what the reference
  * does; it divides.  Used after the frame-sharded reduce. */
 int rt_finish_sum(rt_ctx* ctx, int total_frames);

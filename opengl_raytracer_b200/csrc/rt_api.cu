@@ -77,6 +77,7 @@ struct rt_ctx {
     // targets
     int width = 0, height = 0;
     float4* target[2] = {nullptr, nullptr};
+    float4* peerTarget[2] = {nullptr, nullptr};              // the assembling rank's targets, mapped through CUDA IPC (rt_peer_open)
     int accumIndex = 0;
     int32_t* dIds = nullptr;
     uchar4* dRgba8 = nullptr;
@@ -251,6 +252,10 @@ cudaError_t ensureQueue(rt_ctx* c, bool withWork) {
 void freeTargets(rt_ctx* c) {
     freeQueue(c);
     cudaFree(c->target[0]); cudaFree(c->target[1]); cudaFree(c->dIds); cudaFree(c->dRgba8);
+    for (int i = 0; i < 2; i++) {           // peer mappings are of the old size: a new target means a new rt_peer_open
+        if (c->peerTarget[i]) cudaIpcCloseMemHandle(c->peerTarget[i]);
+        c->peerTarget[i] = nullptr;
+    }
     c->target[0] = c->target[1] = nullptr; c->dIds = nullptr; c->dRgba8 = nullptr;
     c->width = c->height = 0;
     c->accumIndex = 0;
@@ -621,6 +626,11 @@ int renderPass(rt_ctx* c, int frameNumber, int tileX, int tileY, int flags, int 
     P.width = c->width; P.height = c->height;
     const int prev = c->accumIndex, next = 1 - prev;
     P.prev = c->target[prev]; P.next = c->target[next];
+    if (flags & RT_PASS_TO_PEER) {
+        if (!c->peerTarget[0]) return fail(c, RT_ERR_STATE, "RT_PASS_TO_PEER without rt_peer_open");
+        if (sumMode != 0) return fail(c, RT_ERR_INVALID, "RT_PASS_TO_PEER is for tile mode, not for frame sums");
+        P.peerNext = c->peerTarget[next];
+    }
     P.primaryIds = (flags & RT_PASS_PRIMARY_IDS) ? c->dIds : nullptr;
     P.counters = (flags & RT_PASS_COUNTERS) ? c->dCounters : nullptr;
     P.ownedW = ownedCount(c->width, u.tileSizeX, u.numTilesX, tileX);
@@ -924,6 +934,60 @@ static int bandCopy(rt_ctx* c, int tileY, void* dense, int toDense) {
 
 int rt_band_gather(rt_ctx* c, int tileY, void* dense) { return bandCopy(c, tileY, dense, 1); }
 int rt_band_scatter(rt_ctx* c, int tileY, const void* dense) { return bandCopy(c, tileY, const_cast<void*>(dense), 0); }
+
+int rt_peer_export(rt_ctx* c, void* handlesOut) {
+    if (!c || !handlesOut) return RT_ERR_INVALID;
+    if (!c->target[0]) return fail(c, RT_ERR_STATE, "rt_peer_export before rt_target_create");
+    Bind bind(c);
+    static_assert(sizeof(cudaIpcMemHandle_t) == RT_IPC_HANDLE_BYTES, "handle size");
+    for (int i = 0; i < 2; i++) {
+        cudaIpcMemHandle_t h;
+        RT_CUDA(c, cudaIpcGetMemHandle(&h, c->target[i]));
+        memcpy(static_cast<char*>(handlesOut) + i * RT_IPC_HANDLE_BYTES, &h, sizeof h);
+    }
+    return RT_OK;
+}
+
+int rt_peer_close(rt_ctx* c) {
+    if (!c) return RT_ERR_INVALID;
+    Bind bind(c);
+    if (c->peerTarget[0] || c->peerTarget[1]) cudaStreamSynchronize(c->stream);
+    for (int i = 0; i < 2; i++) {
+        if (c->peerTarget[i]) cudaIpcCloseMemHandle(c->peerTarget[i]);
+        c->peerTarget[i] = nullptr;
+    }
+    return RT_OK;
+}
+
+int rt_peer_open(rt_ctx* c, const void* handles) {
+    if (!c || !handles) return RT_ERR_INVALID;
+    if (!c->target[0]) return fail(c, RT_ERR_STATE, "rt_peer_open before rt_target_create");
+    rt_peer_close(c);
+    Bind bind(c);
+    for (int i = 0; i < 2; i++) {
+        cudaIpcMemHandle_t h;
+        memcpy(&h, static_cast<const char*>(handles) + i * RT_IPC_HANDLE_BYTES, sizeof h);
+        void* p = nullptr;
+        const cudaError_t e = cudaIpcOpenMemHandle(&p, h, cudaIpcMemLazyEnablePeerAccess);
+        if (e != cudaSuccess) {
+            cudaGetLastError();
+            rt_peer_close(c);
+            return fail(c, RT_ERR_CUDA, "cudaIpcOpenMemHandle: %s", cudaGetErrorString(e));
+        }
+        c->peerTarget[i] = static_cast<float4*>(p);
+    }
+    return RT_OK;
+}
+
+int rt_peer_is_open(rt_ctx* c) { return c && c->peerTarget[0] ? 1 : 0; }
+
+int rt_target_wait_reads(rt_ctx* c) {
+    if (!c) return RT_ERR_INVALID;
+    if (!c->target[0]) return fail(c, RT_ERR_STATE, "no target");
+    Bind bind(c);
+    waitDownloads(c, 1 - c->accumIndex);
+    return RT_OK;
+}
 
 int rt_timer_start(rt_ctx* c) {
     if (!c) return RT_ERR_INVALID;

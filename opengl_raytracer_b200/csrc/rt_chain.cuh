@@ -20,7 +20,7 @@
 //            the queue while the warp's QUOTA allows (quota = pixels left in the queue / warps in the grid, at most 32: as
 //            the queue drains, warps own fewer pixels and free lanes).  A lane with neither becomes a HELPER: it claims the
 //            next unclaimed offset of the neighbour with the most samples left (within a window of kRing offsets), evaluates
-//            F there and drops (radiance, hits) into that slot's ring in shared memory.  Every lane walks its own chain
+//            F there and drops (radiance, hits) into that slot's ring (global memory, L2-resident).  Every lane walks its own chain
 //            through its ring whenever a SHADE section runs: colour += F(kCur), kCur += hits, in sample order.  An item
 //            whose offset the chain has jumped over is dropped where it stands.
 // So a whole frame on one GPU runs like the persistent kernel (no speculation until the queue holds less than one pixel per
@@ -64,7 +64,6 @@ __global__ void __launch_bounds__(kThreads, 6) rtChainKernel(const __grid_consta
     const bool lambertian = P.lambertian != 0;
     const int leafLanes = P.tune[0] > 0 ? P.tune[0] : RT_VOTE_LEAF_LANES;
     const int shadeLanes = P.tune[1] > 0 ? P.tune[1] : RT_VOTE_SHADE_LANES;
-    const int hitLanes = P.tune[3] > 0 ? P.tune[3] : 6;
     const uint32_t spp = uint32_t(P.raysPerPixel);
     const uint32_t totalWarps = gridDim.x * (kThreads / 32);
     const uint32_t quotaScale = uint32_t(max(P.chainTune[0], 1));      // sixteenths: quota = pixels left * scale / 16 / warps
@@ -112,29 +111,36 @@ __global__ void __launch_bounds__(kThreads, 6) rtChainKernel(const __grid_consta
     bool exhausted = false;                 // warp-uniform: the queue is empty
     uint32_t left = queued;                 // warp-uniform estimate of the pixels left in the queue (last value seen)
 
-    bool pathDone = false;                  // the path ended in the HIT section: the next SHADE section delivers it
     for (;;) {
         const uint32_t mI = __ballot_sync(0xffffffffu, L.mode == MODE_INTERNAL);
         const uint32_t mL = __ballot_sync(0xffffffffu, L.mode == MODE_LEAF);
         const uint32_t mS = __ballot_sync(0xffffffffu, L.mode == MODE_SHADE);
-        const uint32_t mH = __ballot_sync(0xffffffffu, L.mode == MODE_HIT);
-        if ((mI | mL | mS | mH) == 0u) break;  // every lane idle: no slot is active and the queue is empty (see phase 4)
+        if ((mI | mL | mS) == 0u) break;    // every lane idle: no slot is active and the queue is empty (see phase 4)
         RT_STAT(L.mode == MODE_DONE ? stIdle++ : stRefused++);     // (stats build: loop iterations idle / busy)
         RT_STAT(stIters++);
-        const int active = __popc(mI | mL | mS | mH);
+        const int active = __popc(mI | mL | mS);
         const int shadeT = min(shadeLanes, max(1, (active * 3) >> 3));
         const int leafT = min(leafLanes, max(1, active >> 2));
-        const int hitT = min(hitLanes, max(1, active >> 2));
-        if (__popc(mS) >= shadeT || (mI | mL | mH) == 0u) {
+        if (__popc(mS) >= shadeT || (mI | mL) == 0u) {
             // ---------------------------------------------------------------------------------------- SHADE section
-            // phase 1: the ray just traced.  A miss ends the path here (fragment.glsl:342-346); a hit is shaded in the HIT
-            // section, which waits for more of them (under open sky one finished ray in six is a hit: shaded where they
-            // finish, they ran at 2.7 of 32 lanes and cost 9 % of the kernel's instructions)
-            bool done = pathDone;
-            pathDone = false;
-            if (L.mode == MODE_SHADE && !L.needPixel && !done) {
+            // phase 1: the ray just traced -- one iteration of raytrace()'s loop body (fragment.glsl:313-346).  (Shading the
+            // hits in a section of their own that waits for more of them was measured and is slower: 27.3 vs 26.2 ms, the
+            // wait lengthens every chain; profiles/r02_variants.md)
+            bool done = false;
+            if (L.mode == MODE_SHADE && !L.needPixel) {
                 if (L.best.slot >= 0) {
-                    L.mode = MODE_HIT;
+                    const SurfaceHit hit = resolveHit(sc, L.best, L.o, L.d);
+                    const f3 dDiff = diffuseDir(hit.normal, L.seed, lambertian);
+                    const f3 dSpec = reflect3(L.d, hit.normal);
+                    L.d = lerpDir(dDiff, dSpec, hit.roughness);
+                    L.o = add3(hit.point, scale3(hit.normal, 1e-4f));
+                    f3 emitted = scale3(hit.emissionColor, hit.emission);
+                    if (lambertian) emitted = scale3(emitted, 2.0f);
+                    L.incoming = add3(L.incoming, mul3(emitted, L.rayColor));
+                    L.rayColor = mul3(L.rayColor, hit.color);
+                    L.bounce++;
+                    if (hit.emission > 0.0f || L.bounce >= P.nBounces) done = true;
+                    else { beginRay<false>(sc, L, cnt); RT_STAT(stRays++); }
                 } else {
                     L.incoming = add3(L.incoming, sky);   // un-attenuated, as the shader does (:343)
                     done = true;
@@ -176,7 +182,7 @@ __global__ void __launch_bounds__(kThreads, 6) rtChainKernel(const __grid_consta
                 if (sDone >= spp) {
                     const spec::Record r = spec::loadRecord(P, slotPixel);
                     const size_t at = size_t(r.pix >> 16) * size_t(P.width) + size_t(r.pix & 0xffffu);
-                    P.next[at] = accumulate(P, div3(L.color, float(P.raysPerPixel)), at);   // :365, :409-416
+                    storePixel(P, at, accumulate(P, div3(L.color, float(P.raysPerPixel)), at));   // :365, :409-416
                     slotActive = false;
                     slotSerial++;
                 }
@@ -267,23 +273,6 @@ __global__ void __launch_bounds__(kThreads, 6) rtChainKernel(const __grid_consta
                         L.mode = MODE_DONE;     // idle until a SHADE section has something for it
                     }
                 }
-            }
-        } else if (__popc(mH) >= hitT || (mI | mL) == 0u) {
-            // ------------------------------------------------------------------------------------------ HIT section
-            // one iteration of raytrace()'s loop body (fragment.glsl:313-341) for a ray that hit
-            if (L.mode == MODE_HIT) {
-                const SurfaceHit hit = resolveHit(sc, L.best, L.o, L.d);
-                const f3 dDiff = diffuseDir(hit.normal, L.seed, lambertian);
-                const f3 dSpec = reflect3(L.d, hit.normal);
-                L.d = lerpDir(dDiff, dSpec, hit.roughness);
-                L.o = add3(hit.point, scale3(hit.normal, 1e-4f));
-                f3 emitted = scale3(hit.emissionColor, hit.emission);
-                if (lambertian) emitted = scale3(emitted, 2.0f);
-                L.incoming = add3(L.incoming, mul3(emitted, L.rayColor));
-                L.rayColor = mul3(L.rayColor, hit.color);
-                L.bounce++;
-                if (hit.emission > 0.0f || L.bounce >= P.nBounces) { pathDone = true; L.mode = MODE_SHADE; }
-                else { beginRay<false>(sc, L, cnt); RT_STAT(stRays++); }
             }
         } else if (__popc(mL) >= leafT || mI == 0u) {
             if (L.mode == MODE_LEAF) stepLeaf<false>(sc, L, stack, stride, cnt);

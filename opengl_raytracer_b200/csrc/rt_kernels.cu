@@ -124,7 +124,7 @@ __global__ void __launch_bounds__(kBlockThreads) rtPixelKernel(const __grid_cons
         int32_t primaryId = -1;
         const f3 curr = pixelFrame<COUNT, IDS>(P, px, py, st, pc, primaryId);
         const size_t at = size_t(py) * size_t(P.width) + size_t(px);
-        P.next[at] = accumulate(P, curr, at);
+        storePixel(P, at, accumulate(P, curr, at));
         if (IDS) P.primaryIds[at] = primaryId;
     }
     flushCounters<COUNT>(P, pc);

@@ -445,7 +445,7 @@ __global__ void __launch_bounds__(T, 1) rtPoolKernel(const __grid_constant__ Pas
                     }
                     if (pixelEnds) {
                         const size_t at = size_t(s.py) * size_t(P.width) + size_t(s.px);
-                        P.next[at] = accumulate(P, div3(s.color, float(P.raysPerPixel)), at);   // :365, :409-416
+                        storePixel(P, at, accumulate(P, div3(s.color, float(P.raysPerPixel)), at));   // :365, :409-416
                         need = true;
                     }
                 }
@@ -472,7 +472,7 @@ __global__ void __launch_bounds__(T, 1) rtPoolKernel(const __grid_constant__ Pas
                                 s.sample = 0; s.bounce = 0;
                                 if (degenerate) {
                                     const size_t at = size_t(s.py) * size_t(P.width) + size_t(s.px);
-                                    P.next[at] = accumulate(P, div3(zero, float(P.raysPerPixel)), at);
+                                    storePixel(P, at, accumulate(P, div3(zero, float(P.raysPerPixel)), at));
                                     if (IDS) P.primaryIds[at] = -1;
                                     if (COUNT && P.raysPerPixel > 0) cnt[RT_CNT_PATHS] += P.raysPerPixel;
                                 } else {

@@ -97,3 +97,10 @@ RT_DEV float4 accumulate(const PassParams& P, f3 curr, size_t at) {
     }
     return make_float4(out.x, out.y, out.z, 1.0f);
 }
+
+// The pixel's texel.  In peer tile mode (rt_peer_open + RT_PASS_TO_PEER) a second copy goes straight into the assembling
+// rank's target over NVLink — a posted 16-byte store, so the exchange step of tile mode rides on the render kernel.
+RT_DEV void storePixel(const PassParams& P, size_t at, float4 v) {
+    P.next[at] = v;
+    if (P.peerNext != nullptr) P.peerNext[at] = v;
+}

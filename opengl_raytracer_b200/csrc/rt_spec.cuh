@@ -189,7 +189,7 @@ __global__ void __launch_bounds__(kThreads) rtSpecPrimaryKernel(const __grid_con
                 finished = false;
             }
         }
-        if (finished) P.next[at] = accumulate(P, div3(color, float(P.raysPerPixel)), at);   // :365, :409-416
+        if (finished) storePixel(P, at, accumulate(P, div3(color, float(P.raysPerPixel)), at));   // :365, :409-416
         queued = !finished;
     }
     const uint32_t m = __ballot_sync(0xffffffffu, queued);
@@ -430,7 +430,7 @@ __global__ void __launch_bounds__(kThreads) rtSpecChainKernel(const __grid_const
                 }
                 const int px = int(r.pix & 0xffffu), py = int(r.pix >> 16);
                 const size_t at = size_t(py) * size_t(P.width) + size_t(px);
-                P.next[at] = accumulate(P, div3(color, float(P.raysPerPixel)), at);   // :365, :409-416
+                storePixel(P, at, accumulate(P, div3(color, float(P.raysPerPixel)), at));   // :365, :409-416
             }
         }
         const uint32_t m = __ballot_sync(0xffffffffu, again);

@@ -80,6 +80,7 @@ struct PassParams {
     int32_t width, height;
     const float4* prev;
     float4* next;
+    float4* peerNext;               // nullable: the same target on the assembling rank (peer tile mode), written as well
     int32_t* primaryIds;            // nullable
     unsigned long long* counters;   // nullable (RT_CNT_COUNT entries)
     // compact launch domain: the pixels of this tile only

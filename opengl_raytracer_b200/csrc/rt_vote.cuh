@@ -36,7 +36,7 @@ constexpr int kThreads = RT_VOTE_THREADS;
 constexpr int kBurst = RT_VOTE_BURST;
 // per lane: normal0 (3), k0, s1 (3), origin0 (3), incoming0 (3), rayColor0 (3), stop0
 constexpr int kScratchWords = 17;
-constexpr int MODE_INTERNAL = 0, MODE_LEAF = 1, MODE_SHADE = 2, MODE_DONE = 3, MODE_HIT = 4;
+constexpr int MODE_INTERNAL = 0, MODE_LEAF = 1, MODE_SHADE = 2, MODE_DONE = 3;
 
 inline size_t smemBytes(int stackDepth) {
     return size_t(stackDepth) * kThreads * sizeof(uint2) + size_t(kScratchWords) * kThreads * sizeof(uint32_t);
@@ -325,7 +325,7 @@ __global__ void __launch_bounds__(kThreads, COUNT ? 1 : RT_VOTE_MIN_CTAS) rtVote
                 }
                 if (pixelEnds) {
                     const size_t at = size_t(L.py) * size_t(P.width) + size_t(L.px);
-                    P.next[at] = accumulate(P, div3(L.color, float(P.raysPerPixel)), at);   // :365, :409-416
+                    storePixel(P, at, accumulate(P, div3(L.color, float(P.raysPerPixel)), at));   // :365, :409-416
                     L.needPixel = true;
                     L.mode = MODE_SHADE;
                 }
@@ -353,7 +353,7 @@ __global__ void __launch_bounds__(kThreads, COUNT ? 1 : RT_VOTE_MIN_CTAS) rtVote
                             L.sample = 0; L.bounce = 0;
                             if (degenerate) {
                                 const size_t at = size_t(L.py) * size_t(P.width) + size_t(L.px);
-                                P.next[at] = accumulate(P, div3(zero, float(P.raysPerPixel)), at);
+                                storePixel(P, at, accumulate(P, div3(zero, float(P.raysPerPixel)), at));
                                 if (IDS) P.primaryIds[at] = -1;
                                 if (COUNT && P.raysPerPixel > 0) cnt[RT_CNT_PATHS] += P.raysPerPixel;
                                 L.needPixel = true;

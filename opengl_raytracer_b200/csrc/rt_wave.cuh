@@ -81,7 +81,7 @@ __global__ void __launch_bounds__(kThreads) rtPrimaryKernel(const __grid_constan
                 const f3 inc = add3(mk3(0.f, 0.f, 0.f), scale3(mk3(0.1f, 0.6f, 0.92f), P.skyBrightness));
                 for (int s = 0; s < P.raysPerPixel; s++) color = add3(color, inc);
             }
-            P.next[at] = accumulate(P, div3(color, float(P.raysPerPixel)), at);   // :365, :409-416
+            storePixel(P, at, accumulate(P, div3(color, float(P.raysPerPixel)), at));   // :365, :409-416
             if (COUNT && P.raysPerPixel > 0) {
                 pc.v[RT_CNT_PATHS] += P.raysPerPixel;
                 if (casts) {
@@ -208,7 +208,7 @@ __global__ void __launch_bounds__(kThreads) rtPathKernel(const __grid_constant__
             }
             const int px = int(pix & 0xffffu), py = int(pix >> 16);
             const size_t at = size_t(py) * size_t(P.width) + size_t(px);
-            P.next[at] = accumulate(P, div3(color, float(P.raysPerPixel)), at);   // :365, :409-416
+            storePixel(P, at, accumulate(P, div3(color, float(P.raysPerPixel)), at));   // :365, :409-416
         }
     }
     flush<COUNT>(P, pc);

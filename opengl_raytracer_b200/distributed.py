@@ -5,8 +5,11 @@ The path shards two ways, both taken from the reference's own mechanisms:
 * **tile mode** (one frame, many GPUs) — the shader's tile mask (fragment.glsl:382) with ``numTilesX = 1``,
   ``numTilesY = world`` and ``tileSizeY = band_rows`` makes rank g own the interleaved row bands
   ``(y // band_rows) % world == g``: load-balanced, and each pixel is computed exactly as on one GPU, so the
-  assembled frame is bit-identical.  Exchange step: rank 0 gathers every rank's dense band buffer
-  (``rt_band_gather`` -> NCCL gather -> ``rt_band_scatter``).
+  assembled frame is bit-identical.  Exchange step, two ways: **peer** (``open_peer_targets``; same node) — rank 0's
+  targets are mapped into every rank through CUDA IPC and the render kernels store each finished pixel into them over
+  NVLink as well as into their own, so the exchange rides on the pass and all that is left is a 4-byte all-reduce on
+  either side of it as a fence; or **gather** — rank 0 gathers every rank's dense band buffer (``rt_band_gather`` ->
+  NCCL gather -> ``rt_band_scatter``), which works across nodes too.
 * **frame mode** (progressive accumulation) — frames are independent (the seed depends on px, py and
   frameNumber only, fragment.glsl:390): rank g renders frames g, g+world, ... as a running SUM
   (``rt_render_frames_sum``), the sums are added with an NCCL reduce and rank 0 divides by the frame count
@@ -75,14 +78,61 @@ def gather_bands(dist, local_dense, rank: int, world: int, dst: int = 0):
     return bufs
 
 
-def render_tile_mode(ctx, dist, params, rank: int, world: int, frame: int = 0, band_rows: int = 8, dense=None):
+class PeerTargets:
+    """Peer tile mode for one renderer and process group: rank ``dst``'s targets mapped into every other rank."""
+
+    def __init__(self, ctx, dst: int, token):
+        self.ctx, self.dst, self.token = ctx, dst, token
+
+    def close(self):
+        self.ctx.peer_close()
+
+
+def open_peer_targets(ctx, dist, rank: int, world: int, dst: int = 0):
+    """Collective: rank ``dst`` exports its targets (``rt_peer_export``), the others map them (``rt_peer_open``).
+    All ranks must hold targets of one size and have flipped them equally often (checked here; keep issuing the same
+    passes / clears on every rank afterwards).  Returns the ``PeerTargets`` to hand to ``render_tile_mode``, or None
+    where the mapping is refused (different nodes, no peer access) on ANY rank — then use the gather exchange."""
+    import torch
+    state = [None] * world
+    dist.all_gather_object(state, (ctx.width, ctx.height, ctx.accum_index))
+    if len(set(state)) != 1:
+        raise RuntimeError(f"peer tile mode needs equal targets in lockstep on every rank, got {state}")
+    box = [ctx.peer_export() if rank == dst else None]
+    dist.broadcast_object_list(box, src=dst)
+    ok = True
+    if rank != dst:
+        try:
+            ctx.peer_open(box[0])
+        except Exception:                       # RtError: cudaIpcOpenMemHandle refused
+            ok = False
+    flags = [None] * world
+    dist.all_gather_object(flags, ok)
+    if not all(flags):
+        ctx.peer_close()
+        return None
+    token = torch.zeros(1, dtype=torch.int32, device=getattr(ctx, "torch_device", "cpu"))
+    return PeerTargets(ctx, dst, token)
+
+
+def render_tile_mode(ctx, dist, params, rank: int, world: int, frame: int = 0, band_rows: int = 8, dense=None,
+                     peer: PeerTargets | None = None):
     """One frame in tile mode.  ``ctx`` already holds the scene and a width x height target.  Returns the
-    dense buffer used (reusable); on rank 0 the current target then holds the whole frame."""
+    dense buffer used (reusable); on rank 0 the current target then holds the whole frame.  With ``peer`` (from
+    ``open_peer_targets``) no dense buffer is used: the bands land in rank 0's target during the pass."""
     import torch
     p = band_params(params, rank, world, band_rows)
     ctx.set_params(p)
     if world == 1:
         ctx.render_pass(frame, 0, rank, flags=4)                # RT_PASS_SKIP_MASKED
+        return dense
+    if peer is not None:
+        with on_torch_stream(ctx):
+            if rank == peer.dst:
+                ctx.target_wait_reads()                         # a read-back of the target about to be written
+            dist.all_reduce(peer.token)                         # fence: rank dst is done clearing / reading it
+            ctx.render_pass(frame, 0, rank, flags=4 | (8 if rank != peer.dst else 0))   # SKIP_MASKED | TO_PEER
+            dist.all_reduce(peer.token)                         # fence: every rank's pass (and its stores) completed
         return dense
     with on_torch_stream(ctx):
         ctx.render_pass(frame, 0, rank, flags=4)

@@ -54,7 +54,8 @@ class RtParams(ctypes.Structure):
 
 COUNTER_NAMES = ("rays", "rays_traced", "internal", "leaves", "tri_tests", "hits", "pops", "paths")
 VARIANTS = {"auto": 0, "pixel": 1, "persistent": 2, "wavefront": 3, "pool": 4, "samples": 5, "chain": 6}
-PASS_COUNTERS, PASS_PRIMARY_IDS, PASS_SKIP_MASKED = 1, 2, 4
+PASS_COUNTERS, PASS_PRIMARY_IDS, PASS_SKIP_MASKED, PASS_TO_PEER = 1, 2, 4, 8
+IPC_HANDLE_BYTES = 64
 SUM_CONTINUE = 1
 
 _lib = None
@@ -109,6 +110,11 @@ def load_library(path: str | None = None):
         "rt_band_rows": (i, [vp, i]),
         "rt_band_gather": (i, [vp, i, vp]),
         "rt_band_scatter": (i, [vp, i, vp]),
+        "rt_peer_export": (i, [vp, vp]),
+        "rt_peer_open": (i, [vp, vp]),
+        "rt_peer_close": (i, [vp]),
+        "rt_peer_is_open": (i, [vp]),
+        "rt_target_wait_reads": (i, [vp]),
         "rt_finish_sum": (i, [vp, i]),
         "rt_timer_start": (i, [vp]),
         "rt_timer_stop": (i, [vp, P(ctypes.c_float)]),
@@ -322,6 +328,28 @@ class Context:
 
     def band_scatter(self, tileY: int, dense_dev_ptr: int):
         self._check(self.lib.rt_band_scatter(self.handle, tileY, ctypes.c_void_p(dense_dev_ptr)))
+
+    # -- peer tile mode (include/rt_b200.h: the exchange step folded into the render kernels) --
+    def peer_export(self) -> bytes:
+        """CUDA IPC handles of both targets (assembling rank); hand them to the other ranks' ``peer_open``."""
+        buf = ctypes.create_string_buffer(2 * IPC_HANDLE_BYTES)
+        self._check(self.lib.rt_peer_export(self.handle, buf))
+        return buf.raw
+
+    def peer_open(self, handles: bytes):
+        if len(handles) != 2 * IPC_HANDLE_BYTES:
+            raise ValueError(f"expected {2 * IPC_HANDLE_BYTES} bytes of IPC handles, got {len(handles)}")
+        self._check(self.lib.rt_peer_open(self.handle, ctypes.c_char_p(handles)))
+
+    def peer_close(self):
+        self._check(self.lib.rt_peer_close(self.handle))
+
+    @property
+    def peer_is_open(self) -> bool:
+        return bool(self.lib.rt_peer_is_open(self.handle))
+
+    def target_wait_reads(self):
+        self._check(self.lib.rt_target_wait_reads(self.handle))
 
     def timer_start(self):
         self._check(self.lib.rt_timer_start(self.handle))

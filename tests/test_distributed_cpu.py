@@ -104,6 +104,33 @@ class _OracleRenderer:
         img, _, _ = self.oracle.render_pass(*self.scene, p, prev=self.image)
         rows = self._rows(ty)
         self.image[rows] = img[rows]                           # RT_PASS_SKIP_MASKED: only the owned rows are written
+        if flags & 8:                                          # RT_PASS_TO_PEER
+            self.calls[-1] = "render_pass(to_peer)"
+            self.peer_image[rows] = img[rows]
+            self.peer_image.flush()
+
+    # peer tile mode: the 'IPC handle' is the name of a file both processes map
+    accum_index = 0
+    peer_image = None
+
+    def peer_export(self):
+        import tempfile
+        fd, path = tempfile.mkstemp(suffix=".peer")
+        os.close(fd)
+        shared = np.memmap(path, dtype=np.float32, mode="w+", shape=self.image.shape)
+        shared[:] = self.image
+        self.image = shared
+        return path.encode().ljust(128, b"\0")
+
+    def peer_open(self, handles):
+        assert len(handles) == 128
+        self.peer_image = np.memmap(handles.rstrip(b"\0").decode(), dtype=np.float32, mode="r+", shape=self.image.shape)
+
+    def peer_close(self):
+        self.peer_image = None
+
+    def target_wait_reads(self):
+        self.calls.append("target_wait_reads")
 
     def _view(self, ptr, rows):
         import ctypes
@@ -157,6 +184,18 @@ def _mode_worker(rank, world, port, out_dir):
     if rank == 0:
         np.save(os.path.join(out_dir, "tile_mode.npy"), ctx.image)
         assert ctx.calls == ["render_pass", "band_gather", "band_scatter"], ctx.calls
+    # tile mode with the peer exchange: two progressive frames, no gather; the fences are the group's all-reduces
+    ctx = _OracleRenderer(oracle, tris, boxes, indices, cfg.width, cfg.height)
+    peer = distributed.open_peer_targets(ctx, dist, rank, world)
+    assert peer is not None
+    for frame in (0, 1):
+        distributed.render_tile_mode(ctx, dist, params, rank, world, frame=frame, band_rows=4, peer=peer)
+    if rank == 0:
+        np.save(os.path.join(out_dir, "tile_mode_peer.npy"), np.asarray(ctx.image))
+        assert ctx.calls == ["target_wait_reads", "render_pass"] * 2, ctx.calls
+    else:
+        assert ctx.calls == ["render_pass(to_peer)"] * 2, ctx.calls
+    peer.close()
     # frame mode in two instalments: frames 0..2, then 3..6 continued from rank 0's running mean
     ctx = _OracleRenderer(oracle, tris, boxes, indices, cfg.width, cfg.height)
     view = lambda c: torch.from_numpy(c.image)
@@ -181,6 +220,8 @@ def test_render_modes_through_the_public_functions(tmp_path, oracle_mod):
     params = cfg.params()
     single, _, _ = oracle_mod.render_pass(tris, boxes, indices, params)
     assert np.load(tmp_path / "tile_mode.npy").tobytes() == single.tobytes()
+    two = oracle_mod.render_frames(tris, boxes, indices, params, 0, 2)
+    assert np.load(tmp_path / "tile_mode_peer.npy").tobytes() == two.tobytes()
     mean = oracle_mod.render_frames(tris, boxes, indices, params, 0, 7)
     got = np.load(tmp_path / "frame_mode.npy")
     assert np.abs(got[..., :3] - mean[..., :3]).max() < 2e-5 and (got[..., 3] == 1).all()
