@@ -420,7 +420,10 @@ def run_gpu(args):
     ppath = os.path.join(ROOT, "profiles", "bench_kernel_counters.json")
     if os.path.isfile(ppath):
         with open(ppath) as f:
-            prof = json.load(f).get(f"{WORKLOAD}/{variant}", {})
+            table = json.load(f)
+        # a rank's 1/N share runs its own mix of kernels (SAMPLES rounds): its capture is keyed by the share
+        prof = table.get(f"{WORKLOAD}/{variant}/share{world}" if world > 1 else f"{WORKLOAD}/{variant}", {})
+    per_rank = 1        # the captures are of exactly what rank 0 runs (its 1/N share for N > 1): nothing to divide
     clock_mhz = (main["clocks"] or {}).get("sm_mhz") or sm_max
     # What bounds this path.  The scene (8 MB) is L2/L1-resident by design, DRAM traffic is the framebuffer only, so the
     # HBM roofline does not bind; the ceilings that do are on the SM: the L1 data pipe (one wavefront per 128-byte line
@@ -433,14 +436,14 @@ def run_gpu(args):
     subs = {}
     if prof.get("inst_executed_per_launch"):
         peak_issue = measured.get("issue_gwarpinst_s", 0.0) * 1e9 or sm_count * 4 * clock_mhz * 1e6
-        ach = prof["inst_executed_per_launch"] / world / (main["kernel_ms"] * 1e-3)     # N > 1: this rank's 1/N share (approx.)
+        ach = prof["inst_executed_per_launch"] / per_rank / (main["kernel_ms"] * 1e-3)
         subs["issue"] = {"achieved": ach / 1e9, "peak": peak_issue / 1e9, "unit": "G warp-inst/s", "frac": ach / peak_issue,
                          "lanes_per_inst": prof.get("lanes_per_inst"), "peak_nominal": sm_count * 4 * clock_mhz * 1e-3,
                          "source": "inst per launch from the committed ncu capture of this workload, time live; "
                                    "peak = FFMA issue micro-benchmark on this GPU (nominal: 4 schedulers x SMs x clock)"}
     if prof.get("l1_wavefronts_per_launch"):
         peak_wf = measured.get("l1_gwavefronts_s", 0.0) * 1e9 or sm_count * clock_mhz * 1e6
-        ach = prof["l1_wavefronts_per_launch"] / world / (main["kernel_ms"] * 1e-3)
+        ach = prof["l1_wavefronts_per_launch"] / per_rank / (main["kernel_ms"] * 1e-3)
         subs["l1_wavefronts"] = {"achieved": ach / 1e9, "peak": peak_wf / 1e9, "unit": "G wavefronts/s", "frac": ach / peak_wf,
                                  "peak_nominal": sm_count * clock_mhz * 1e-3,
                                  "source": "l1tex data-pipe wavefronts per launch from the committed ncu capture, time live; "
@@ -454,7 +457,7 @@ def run_gpu(args):
         # the scene data comes from L1/L2: L2 -> SM bandwidth is the memory ceiling the algorithmic bytes can be held against
         algorithmic["l2_peak"] = measured["l2_gbs"]
         algorithmic["ratio_to_l2_peak"] = achieved / measured["l2_gbs"]
-    traffic = (prof["dram_bytes_per_launch"] / world) if prof.get("dram_bytes_per_launch") else None
+    traffic = (prof["dram_bytes_per_launch"] / per_rank) if prof.get("dram_bytes_per_launch") else None
     if subs:
         name = max(subs, key=lambda k: subs[k]["frac"])
         roofline = {"bound": name, "achieved": subs[name]["achieved"], "peak": subs[name]["peak"], "unit": subs[name]["unit"],
