@@ -14,7 +14,7 @@ import torch.multiprocessing as mp
 
 pytestmark = pytest.mark.gpu
 
-W, H, SPP, FRAMES, BANDS = 320, 200, 4, 2, 8
+W, H, SPP, FRAMES, BANDS = 320, 200, 4, 3, 8
 SCENE = "rects_box"
 
 
@@ -62,9 +62,16 @@ def _worker(rank, world, port, out_dir, backend, variant):
     peer = distributed.open_peer_targets(ctx, group, rank, world)
     assert peer is not None, "cudaIpcOpenMemHandle refused between two processes of one box"
     assert ctx.peer_is_open == (rank != 0)
+    # rank 0 reads every frame back asynchronously while the next ones render: frame f + 2 is written into the target
+    # frame f is being copied out of, by the peers too, so the fence before the pass must wait for that copy
+    stage = [torch.empty((H, W, 4), dtype=torch.float32).pin_memory() for _ in range(FRAMES)] if rank == 0 else []
     for frame in range(FRAMES):
         distributed.render_tile_mode(ctx, group, params, rank, world, frame=frame, band_rows=BANDS, peer=peer)
+        if rank == 0:
+            ctx.read_accum_f32_async(stage[frame].data_ptr())
     if rank == 0:
+        ctx.read_wait()
+        np.save(os.path.join(out_dir, "frames.npy"), np.stack([t.numpy() for t in stage]))
         np.save(os.path.join(out_dir, "peer.npy"), ctx.read_accum_f32())
     else:
         # a pass that asks for the peer copy after the mapping is gone is refused, not silently local
@@ -84,17 +91,21 @@ def _single(variant):
     ctx.scene_upload(tris, boxes, indices)
     ctx.set_params(params)
     ctx.target_create(W, H)
-    ctx.render_frames(0, FRAMES)
-    out = ctx.read_accum_f32()
+    frames = []
+    for frame in range(FRAMES):
+        ctx.render_pass(frame, 0, 0)
+        frames.append(ctx.read_accum_f32())
     ctx.close()
-    return out
+    return np.stack(frames)
 
 
 @pytest.mark.parametrize("variant", ["auto", "pixel", "persistent", "wavefront", "pool", "samples", "chain"])
 def test_peer_tile_mode_two_processes_one_device(tmp_path, variant):
     port = 32500 + os.getpid() % 2000
     mp.spawn(_worker, args=(2, port, str(tmp_path), "gloo", variant), nprocs=2, join=True)
-    assert np.load(tmp_path / "peer.npy").tobytes() == _single(variant).tobytes()
+    single = _single(variant)
+    assert np.load(tmp_path / "peer.npy").tobytes() == single[-1].tobytes()
+    assert np.load(tmp_path / "frames.npy").tobytes() == single.tobytes()      # each frame as read back on the way
 
 
 def test_peer_tile_mode_over_nccl(tmp_path):
@@ -104,4 +115,6 @@ def test_peer_tile_mode_over_nccl(tmp_path):
         pytest.skip("one GPU: the NCCL leg needs a rank per device")
     port = 34500 + os.getpid() % 2000
     mp.spawn(_worker, args=(world, port, str(tmp_path), "nccl", "auto"), nprocs=world, join=True)
-    assert np.load(tmp_path / "peer.npy").tobytes() == _single("auto").tobytes()
+    single = _single("auto")
+    assert np.load(tmp_path / "peer.npy").tobytes() == single[-1].tobytes()
+    assert np.load(tmp_path / "frames.npy").tobytes() == single.tobytes()
