@@ -54,3 +54,29 @@ def test_no_cpu_fallback_without_gpu():
         rtlib.Context(0)
     with pytest.raises(RuntimeError):
         rtlib.load_library(os.path.join(ROOT, "does_not_exist.so"))
+
+
+def test_every_entry_point_rejects_a_null_context():
+    """Argument validation happens before anything touches CUDA, so it can be checked without a GPU: every function that
+    takes the context refuses NULL (error code, null pointer or no-op) instead of dereferencing it."""
+    if not os.path.isfile(rtlib.LIB_PATH):
+        pytest.skip("librt_b200.so not built")
+    text = open(os.path.join(ROOT, "include", "rt_b200.h")).read()
+    text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
+    protos = re.findall(r"^\s*(int|void\s*\*|const char\s*\*|void)\s+(rt_[a-z0-9_]+)\s*\(\s*rt_ctx\s*\*", text, flags=re.M)
+    assert len(protos) >= 40, len(protos)
+    lib = ctypes.CDLL(rtlib.LIB_PATH)
+    null = ctypes.c_void_p(None)
+    for ret, name in protos:
+        fn = getattr(lib, name)
+        kind = ret.replace(" ", "")
+        fn.restype = ctypes.c_int if kind == "int" else None if kind == "void" else ctypes.c_void_p
+        out = fn(null, null, null, null, null, null, null)        # the other arguments are never looked at
+        if name in ("rt_last_pass_launches", "rt_peer_is_open"):
+            assert out == 0, name                                   # queries: "none"
+        elif kind == "int":
+            assert out != 0, f"{name}(NULL) returned RT_OK"
+        elif name == "rt_last_error":
+            assert ctypes.string_at(out), "rt_last_error(NULL) names the problem"      # a static message, not a crash
+        elif kind != "void":
+            assert not out, f"{name}(NULL) returned a pointer"
