@@ -495,3 +495,28 @@ def test_samples_offsets_beyond_the_jump_tables(ctx, oracle_mod, scene_buffers, 
     acc, _, cnt = oracle_mod.render_pass(tris, boxes, indices, params, want_counters=True)
     assert cnt["hits"] // (6 * 4) > 16384                     # the offsets really do leave the tables
     assert got.tobytes() == acc.tobytes(), f"{(got != acc).any(-1).sum()} pixels differ"
+
+
+@pytest.mark.parametrize("seed", range(24))
+@pytest.mark.parametrize("variant", ["auto"] + VARIANTS)
+def test_random_scenes_match_oracle(ctx, oracle_mod, seed, variant):
+    """Seeded random scenes (conftest.random_scene: boxes, slabs, mirrors, emitters; random bounces, samples, lambertian,
+    sky, jitter, ragged sizes, tiling), two progressive frames in the reference's tile order: every variant bit-exact."""
+    from conftest import random_scene
+    tris, boxes, indices, params = random_scene(seed)
+    got = _render_gpu(ctx, tris, boxes, indices, params, 2, variant)
+    want = oracle_mod.render_frames(tris, boxes, indices, params, 0, 2)
+    assert got.tobytes() == want.tobytes(), f"{(got != want).any(-1).sum()} pixels differ"
+
+
+@pytest.mark.parametrize("seed", range(24))
+@pytest.mark.parametrize("variant", ["samples", "chain"])
+def test_random_scenes_with_speculation_forced(ctx, oracle_mod, monkeypatch, seed, variant):
+    """The same scenes with the device-side gate overridden: the speculating variants evaluate samples ahead of the chain
+    even where most pixels hit (emitters end paths early, mirrors and rooms make them long) and stay bit-exact."""
+    from conftest import random_scene
+    monkeypatch.setenv("RT_VOTE_TUNE", "0,0,1")
+    tris, boxes, indices, params = random_scene(seed)
+    got = _render_gpu(ctx, tris, boxes, indices, params, 2, variant)
+    want = oracle_mod.render_frames(tris, boxes, indices, params, 0, 2)
+    assert got.tobytes() == want.tobytes(), f"{(got != want).any(-1).sum()} pixels differ"

@@ -103,6 +103,21 @@ def test_oracle_matches_reference_shader_build(oracle_mod, scene_buffers, scene,
     assert port.tobytes() == ref.tobytes()
 
 
+@pytest.mark.parametrize("seed", range(24))
+def test_oracle_matches_reference_shader_build_on_random_scenes(oracle_mod, seed):
+    """The pin widened beyond the named scenes: seeded random boxes, materials and uniforms (conftest.random_scene), two
+    progressive frames with the reference's tile loop — the port and the reference's own shader source compiled as C++
+    agree bit for bit."""
+    if not oracle_mod.have_ref():
+        pytest.skip("oracle/_ref/libfragment_ref.so not built (needs /root/reference)")
+    from conftest import random_scene
+    tris, boxes, indices, params = random_scene(seed)
+    port = oracle_mod.render_frames(tris, boxes, indices, params, 0, 2, impl="port")
+    ref = oracle_mod.render_frames(tris, boxes, indices, params, 0, 2, impl="ref")
+    assert np.isfinite(port[..., 3]).all()
+    assert port.tobytes() == ref.tobytes()
+
+
 def test_oracle_counters_are_consistent(oracle_mod, scene_buffers):
     tris, boxes, indices, cfg = scene_buffers("rects_box")
     params = cfg.scaled(64, 36, 2).params()
