@@ -38,6 +38,13 @@ class _HostFencedGroup:
         self.dist.all_reduce(self.cpu_token)
 
 
+def _free_port():
+    import socket
+    with socket.socket() as sock:
+        sock.bind(("127.0.0.1", 0))
+        return sock.getsockname()[1]
+
+
 def _scene():
     from opengl_raytracer_b200 import configs
     from opengl_raytracer_b200.scene import Scene
@@ -101,7 +108,7 @@ def _single(variant):
 
 @pytest.mark.parametrize("variant", ["auto", "pixel", "persistent", "wavefront", "pool", "samples", "chain"])
 def test_peer_tile_mode_two_processes_one_device(tmp_path, variant):
-    port = 32500 + os.getpid() % 2000
+    port = _free_port()
     mp.spawn(_worker, args=(2, port, str(tmp_path), "gloo", variant), nprocs=2, join=True)
     single = _single(variant)
     assert np.load(tmp_path / "peer.npy").tobytes() == single[-1].tobytes()
@@ -113,7 +120,7 @@ def test_peer_tile_mode_over_nccl(tmp_path):
     world = min(torch.cuda.device_count(), 4)
     if world < 2:
         pytest.skip("one GPU: the NCCL leg needs a rank per device")
-    port = 34500 + os.getpid() % 2000
+    port = _free_port()
     mp.spawn(_worker, args=(world, port, str(tmp_path), "nccl", "auto"), nprocs=world, join=True)
     single = _single("auto")
     assert np.load(tmp_path / "peer.npy").tobytes() == single[-1].tobytes()

@@ -20,3 +20,4 @@ with rtlib.Context(0) as ctx:
     for i in range(passes):
         ctx.target_clear(); ctx.timer_start(); ctx.render_pass(0, 0, 0, flags=4 if bands > 1 else 0)
         print(name, variant, f"bands={bands}", "tune=" + os.environ.get("RT_VOTE_TUNE", "-"), "ms", round(ctx.timer_stop(), 3), flush=True)
+    print("ran:", ctx.last_pass_variant(), "launches per pass:", ctx.last_pass_launches(), flush=True)
