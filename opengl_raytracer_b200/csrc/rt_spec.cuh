@@ -20,7 +20,8 @@
 //   stage 3  rtSpecChainKernel    per pixel: follow the chain through the table, add in sample order, write the
 //                                 pixel.  A chain that leaves the table continues by evaluating F on demand.
 // Cost: F is evaluated for every k < K but only every hits-th is used, so the work grows by the mean hit count per
-// path: 1.07 under open sky (worth it: the frame becomes embarrassingly parallel), 4.7 in a closed room (not worth
+// path: 1.21 under open sky (worth it for a small share of a frame, which becomes embarrassingly parallel; a whole frame
+// is better served by rt_chain.cuh), 4.7 in a closed room (not worth
 // it).  The mode is decided ON THE DEVICE from stage 1's hit fraction (vote::samplesSpeculate): when more than a
 // quarter of the pixels hit, stage 2 exits at once and stage 3 evaluates every sample on demand — the plain sequential
 // pixel-frame — or, under AUTO (PassParams::specGate), leaves the pass to the persistent kernel launched behind it.

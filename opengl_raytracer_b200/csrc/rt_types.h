@@ -6,7 +6,7 @@
 //
 // Records are 32-byte aligned and fetched with 256-bit loads (ld.global.nc.v8.f32 = LDG.E.256, sm_100+): the L1 data pipe
 // charges a divergent load one wavefront per 128-byte line per INSTRUCTION whatever its width, so a 64-byte node costs
-// two wavefronts per lane instead of four (profiles/r02_ldg256.md: 200 G vs 120 G records/s L1-resident).
+// two wavefronts per lane instead of four (profiles/r02_variants.md §1: 200 G vs 120 G records/s L1-resident).
 //
 //   NodeRec  64 B  one per REACHABLE internal node: the bounds of BOTH children (the shader slab-tests
 //                  both children when it expands a node, fragment.glsl:285-287) + two child references.
