@@ -1,4 +1,4 @@
-// ldg256_probe.cu — micro-benchmark behind the node/triangle record loads of librt_b200 (profiles/r02_ldg256.md).
+// ldg256_probe.cu — micro-benchmark behind the node/triangle record loads of librt_b200 (profiles/r02_variants.md section 1).
 // Every lane of a warp reads one 64-byte record at an unrelated index of a window (what a node step does), either as
 // 4 x LDG.128 or as 2 x LDG.256 (ld.global.nc.v8.f32, sm_100+).  Reports records/s for an L1-resident and an
 // L2-resident window.  build: nvcc -gencode arch=compute_100a,code=sm_100a -O3 -o ldg256_probe ldg256_probe.cu
