@@ -438,6 +438,17 @@ cudaError_t rtLaunchSamples(const PassParams& Pin, bool ids, int sms, uint32_t* 
 int rtChainMaxBlocksPerSm() { return 8; }
 size_t rtChainRingBytes(int sms) { return chain::ringBytes(sms * rtChainMaxBlocksPerSm()); }
 
+namespace {
+// ring entry e of lane t <- "F(k) = 1e9 with one hit" for k = e, e + kRing, e + 2 kRing or e + 3 kRing (by lane)
+__global__ void rtChainPoisonKernel(float4* ring, size_t entries) {
+    for (size_t i = blockIdx.x * size_t(blockDim.x) + threadIdx.x; i < entries; i += size_t(gridDim.x) * blockDim.x) {
+        const uint32_t e = uint32_t(i % chain::kRing), t = uint32_t(i / chain::kRing);
+        const uint32_t k = e + chain::kRing * (t & 3u);
+        ring[i] = make_float4(1e9f, 1e9f, 1e9f, __uint_as_float(((k + 1u) << chain::kHitBits) | 1u));
+    }
+}
+}  // namespace
+
 cudaError_t rtLaunchChain(const PassParams& Pin, bool ids, int sms, cudaStream_t stream) {
     PassParams P = Pin;
     if (P.ownedW <= 0 || P.ownedH <= 0) return cudaSuccess;
@@ -488,6 +499,11 @@ cudaError_t rtLaunchChain(const PassParams& Pin, bool ids, int sms, cudaStream_t
     const long long pixels = (long long)P.ownedW * P.ownedH;
     const long long want = (pixels + chain::kThreads - 1) / chain::kThreads;
     const int gridChain = int(std::min<long long>((long long)sms * perSm, std::max<long long>(want, 1)));
+    if (getenv("RT_CHAIN_POISON")) {
+        // test aid (tests/test_gpu_parity.py): the rings are never initialised — a slot clears its own at its first help — so
+        // fill them with entries that LOOK like results of small offsets; a read before the clear would poison the image
+        rtChainPoisonKernel<<<sms * 8, 256, 0, stream>>>(P.chainRing, size_t(gridChain) * chain::kThreads * chain::kRing);
+    }
     chain::rtChainKernel<<<gridChain, chain::kThreads, smemChain, stream>>>(P);
     return cudaGetLastError();
 }

@@ -520,3 +520,18 @@ def test_random_scenes_with_speculation_forced(ctx, oracle_mod, monkeypatch, see
     got = _render_gpu(ctx, tris, boxes, indices, params, 2, variant)
     want = oracle_mod.render_frames(tris, boxes, indices, params, 0, 2)
     assert got.tobytes() == want.tobytes(), f"{(got != want).any(-1).sum()} pixels differ"
+
+
+@pytest.mark.parametrize("scene,w,h,spp,over", [("cfg4_open", 192, 108, 24, {}), ("cfg1_open", 160, 90, 16, {}),
+                                                ("rects_box", 64, 36, 12, {"bounces": 5})])
+def test_chain_rings_are_never_read_before_they_are_cleared(ctx, oracle_mod, scene_buffers, monkeypatch, scene, w, h, spp, over):
+    """The chain variant's rings live in uninitialised global memory; a slot clears its own ring at its first help.
+    RT_CHAIN_POISON fills them beforehand with entries that look like valid results of small offsets (radiance 1e9): any
+    read before the clear, or of an entry left by an earlier pixel, would show in the image.  Speculation forced on."""
+    monkeypatch.setenv("RT_CHAIN_POISON", "1")
+    monkeypatch.setenv("RT_VOTE_TUNE", "0,0,1")
+    tris, boxes, indices, cfg = scene_buffers(scene)
+    params = cfg.scaled(w, h, spp).params(**over)
+    got = _render_gpu(ctx, tris, boxes, indices, params, 2, "chain")
+    want = oracle_mod.render_frames(tris, boxes, indices, params, 0, 2)
+    assert got.tobytes() == want.tobytes(), f"{(got != want).any(-1).sum()} pixels differ"
