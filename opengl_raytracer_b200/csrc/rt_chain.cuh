@@ -37,6 +37,11 @@
 
 namespace chain {
 
+#ifdef RT_CHAIN_STATS
+__device__ unsigned long long gTimelineStart;
+__device__ unsigned int gTimeline[3][256];      // per 0.25 ms of the kernel: evaluations started, samples consumed, pixels finished
+#endif
+
 constexpr int kThreads = 128;
 constexpr int kRing = 32;                  // ring entries per slot: offsets [kCur, kCur + window), window <= kRing, can be claimed
 constexpr int kHitBits = 6;                // ring tag = (k + 1) << kHitBits | hits: nBounces < 64 (the host checks)
@@ -45,6 +50,7 @@ constexpr int kHitBits = 6;                // ring tag = (k + 1) << kHitBits | h
 // owner's own result stays in registers — so a whole frame on one GPU reads no ring until its tail.
 inline size_t smemBytes(int stackDepth) { return size_t(stackDepth) * kThreads * sizeof(uint2); }
 inline size_t ringBytes(int gridBlocks) { return size_t(gridBlocks) * kThreads * kRing * sizeof(float4); }
+
 
 __global__ void __launch_bounds__(kThreads, 6) rtChainKernel(const __grid_constant__ PassParams P) {
     extern __shared__ uint2 smem[];
@@ -85,12 +91,26 @@ __global__ void __launch_bounds__(kThreads, 6) rtChainKernel(const __grid_consta
     }
     uint32_t cnt[RT_CNT_COUNT];   // unused (COUNT = false), keeps the shared step functions' signature
 #ifdef RT_CHAIN_STATS
+    {
+        unsigned long long t;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+        atomicCAS(&gTimelineStart, 0ull, t);
+    }
+    const unsigned long long stStart = *reinterpret_cast<volatile unsigned long long*>(&gTimelineStart);
+#define RT_TIMELINE(which)                                                                   \
+    do {                                                                                     \
+        unsigned long long t_;                                                               \
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_));                               \
+        const unsigned long long bin_ = (t_ - stStart) / 250000ull;                          \
+        atomicAdd(&gTimeline[which][bin_ < 255ull ? bin_ : 255ull], 1u);                     \
+    } while (0)
     uint32_t stStarted = 0, stOwn = 0, stRefused = 0, stDropped = 0, stRays = 0, stIdle = 0, stSections = 0, stUsed = 0, stIters = 0;
     unsigned long long stT0;
     asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(stT0));
 #define RT_STAT(x) (x)
 #else
 #define RT_STAT(x) ((void)0)
+#define RT_TIMELINE(which) ((void)0)
 #endif
 
     Lane L;
@@ -156,7 +176,7 @@ __global__ void __launch_bounds__(kThreads, 6) rtChainKernel(const __grid_consta
                         L.color = add3(L.color, L.incoming);
                         kCur += uint32_t(L.bounce);
                         sDone++;
-                        RT_STAT(stUsed++);
+                        RT_STAT(stUsed++); RT_TIMELINE(1);
                     } else if (tSerial == itemSerial && itemK >= tK) {
                         __stcg(warpRing + itemLane * kRing + (itemK & (kRing - 1)),
                                make_float4(L.incoming.x, L.incoming.y, L.incoming.z, __uint_as_float(((itemK + 1u) << kHitBits) | uint32_t(L.bounce))));
@@ -175,7 +195,7 @@ __global__ void __launch_bounds__(kThreads, 6) rtChainKernel(const __grid_consta
                         L.color = add3(L.color, mk3(f.x, f.y, f.z));      // trace(), :359
                         kCur += tag & ((1u << kHitBits) - 1u);
                         sDone++;
-                        RT_STAT(stUsed++);
+                        RT_STAT(stUsed++); RT_TIMELINE(1);
                     }
                 }
                 nextK = max(nextK, kCur);
@@ -185,6 +205,7 @@ __global__ void __launch_bounds__(kThreads, 6) rtChainKernel(const __grid_consta
                     storePixel(P, at, accumulate(P, div3(L.color, float(P.raysPerPixel)), at));   // :365, :409-416
                     slotActive = false;
                     slotSerial++;
+                    RT_TIMELINE(2);
                 }
             }
             // phase 3: an item whose offset the chain has passed, or whose pixel is finished, is dropped where it stands
@@ -268,7 +289,7 @@ __global__ void __launch_bounds__(kThreads, 6) rtChainKernel(const __grid_consta
                         L.rayColor = r.rayColor0;
                         L.bounce = 1;
                         beginRay<false>(sc, L, cnt);
-                        RT_STAT(stStarted++); RT_STAT(stRays++);
+                        RT_STAT(stStarted++); RT_STAT(stRays++); RT_TIMELINE(0);
                     } else {
                         L.mode = MODE_DONE;     // idle until a SHADE section has something for it
                     }

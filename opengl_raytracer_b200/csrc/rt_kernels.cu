@@ -479,8 +479,25 @@ cudaError_t rtLaunchChain(const PassParams& Pin, bool ids, int sms, cudaStream_t
             fprintf(stderr, "   warp iterations max %llu sum %llu; warp life max %.3f ms, sum %.1f ms; lives in 2 ms bins:", x[0], x[1], x[2] * 1e-6, x[3] * 1e-6);
             for (int i = 0; i < 8; i++) fprintf(stderr, " %llu", x[4 + i]);
             fprintf(stderr, "\n");
+            static unsigned int tl[3][256];
+            cudaMemcpyFromSymbol(tl, chain::gTimeline, sizeof tl);
+            const char* names[3] = {"started ", "consumed", "finished"};
+            for (int w = 0; w < 3; w++) {
+                fprintf(stderr, "   timeline %s per 0.25 ms:", names[w]);
+                int last = 255;
+                while (last > 0 && tl[w][last] == 0) last--;
+                for (int i = 0; i <= last; i++) fprintf(stderr, " %u", tl[w][i]);
+                fprintf(stderr, "\n");
+            }
         }
     } printer{P, stream};
+    {
+        static unsigned int zeros[3][256];
+        unsigned long long z = 0;
+        cudaMemcpyToSymbolAsync(chain::gTimeline, zeros, sizeof zeros, 0, cudaMemcpyHostToDevice, stream);
+        cudaMemcpyToSymbolAsync(chain::gTimelineStart, &z, sizeof z, 0, cudaMemcpyHostToDevice, stream);
+        cudaStreamSynchronize(stream);
+    }
 #endif
     if (ids) spec::rtSpecPrimaryKernel<true><<<grid, spec::kThreads, smem, stream>>>(P);
     else spec::rtSpecPrimaryKernel<false><<<grid, spec::kThreads, smem, stream>>>(P);
