@@ -391,6 +391,7 @@ cudaError_t rtLaunchSamples(const PassParams& Pin, bool ids, int sms, uint32_t* 
     PassParams P = Pin;
     if (P.ownedW <= 0 || P.ownedH <= 0) return cudaSuccess;
     if (const char* e = getenv("RT_VOTE_TUNE")) sscanf(e, "%d,%d,%d", &P.tune[0], &P.tune[1], &P.tune[2]);
+    if (const char* e = getenv("RT_SPEC_MARGIN")) { int a = 0, b = 0; if (sscanf(e, "%d,%d", &a, &b) == 2) P.tune[3] = (a << 8) | (b & 255); }
     // workCounters, todoCount and classCount are one array (rt_api.cu): cleared with one memset
     cudaError_t e = cudaMemsetAsync(P.workCounters, 0, size_t(kSpecWorkUints) * sizeof(unsigned int), stream);
     if (e != cudaSuccess) return e;

@@ -62,17 +62,24 @@ RT_DEV uint32_t jumpSeed(uint32_t seed, unsigned int k) {
     return jumpBlocks(s, h, cJumpHi[1]);
 }
 
-// Table sizes.  Round 0 gives every queued pixel rays_per_pixel samples at up to 1.25 hits each (open-sky chains run
+// Table sizes.  Round 0 gives every queued pixel rays_per_pixel samples at up to 1.15 hits each (open-sky chains run
 // at 1.0-1.3).  A chain that leaves its table knows its own rate (hits so far / samples so far), so the pixel asks for
-// what its remaining samples should need, with a margin, rounded up to a size class (8, 12, 16, 24, 32, 48, ...); the
+// what its remaining samples should need, with a margin, rounded up to a size class (8, 10, 12, 14, 16, 20, ...); the
 // last round asks for the bound (remaining samples x nBounces hits), which always suffices.  A round is then ONE
 // evaluation launch over all classes, and a 64-spp frame is done in three rounds where fixed doubling top-ups took
 // six (each of which costs at least one path latency, 0.3 ms, however few pixels are left).
-constexpr int kClasses = 22;
-constexpr int kClassStride = 32;             // uints per round in PassParams::classCount: [c] pixels of class c, [30] entries reserved
-constexpr int kReserved = 30;
-__host__ __device__ inline unsigned int classK(int c) { return ((c & 1) ? 12u : 8u) << (c >> 1); }
-inline int laterK(int raysPerPixel) { return raysPerPixel / 4 > 8 ? (raysPerPixel / 4 < 256 ? raysPerPixel / 4 : 256) : 8; }
+// Size classes, four per octave: 8, 10, 12, 14, 16, 20, 24, 28, 32, 40, ... — a chain is given at most 1.25 x what it asked
+// for (two per octave, round 1, gave up to 1.5 x; with the tighter margins below: 1/2, 1/4, 1/8 share of the 4K dragon
+// frame 15.6 / 8.47 / 4.60 -> 15.0 / 8.05 / 4.49 ms, profiles/r02_variants.md).
+constexpr int kClasses = 44;
+constexpr int kClassStride = 64;             // uints per round in PassParams::classCount: [c] pixels of class c, [62] entries reserved
+constexpr int kReserved = 62;
+constexpr int kClassBits = 6;                // chainClass = rank << kClassBits | class
+__host__ __device__ inline unsigned int classK(int c) { return (4u + (unsigned int)(c & 3)) << ((c >> 2) + 1); }
+inline int laterK(int raysPerPixel) {      // round 0's allowance over one hit per sample: 15 % (measured best of 0-25 %)
+    const int k = (raysPerPixel * 3 + 10) / 20;
+    return k > 8 ? (k < 256 ? k : 256) : 8;
+}
 inline int tableK(int raysPerPixel) {
     const int k = raysPerPixel + laterK(raysPerPixel);
     return k < kMaxK / 4 ? k : kMaxK / 4;
@@ -405,7 +412,10 @@ __global__ void __launch_bounds__(kThreads) rtSpecChainKernel(const __grid_const
                 const unsigned long long bound = rem * (unsigned long long)max(P.nBounces, 1);
                 unsigned long long need = bound;
                 if (round + 2 < kRounds && s > 0) {
-                    const float predicted = float(k) / float(s) * float(rem) * 1.125f + 2.0f * sqrtf(float(rem)) + 2.0f;
+                    // margins: tune[3] = (per-mille factor << 8) | (tenths of sqrt(rem)); 0 = the defaults
+                    const float mFactor = P.tune[3] > 0 ? float(P.tune[3] >> 8) * 1e-3f : 1.03f;
+                    const float mSqrt = P.tune[3] > 0 ? float(P.tune[3] & 255) * 0.1f : 1.0f;
+                    const float predicted = float(k) / float(s) * float(rem) * mFactor + mSqrt * sqrtf(float(rem)) + 2.0f;
                     need = min(bound, (unsigned long long)predicted);
                 }
                 int cls = 0;
@@ -417,7 +427,7 @@ __global__ void __launch_bounds__(kThreads) rtSpecChainKernel(const __grid_const
                         const unsigned int rank = atomicAdd(nextClass + cls, 1u);
                         P.chainColor[j] = make_float4(color.x, color.y, color.z, __int_as_float(s));
                         P.chainK[j] = k;
-                        P.chainClass[j] = (rank << 5) | (unsigned int)cls;
+                        P.chainClass[j] = (rank << kClassBits) | (unsigned int)cls;
                         again = true;
                     } else {
                         atomicSub(nextClass + kReserved, Kc);   // the buffer is full: this pixel finishes below
@@ -460,7 +470,7 @@ __global__ void __launch_bounds__(kThreads) rtSpecSortKernel(const __grid_consta
     const unsigned int n = P.todoCount[round];
     for (unsigned int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
         const unsigned int j = P.todoFlat[i], cr = P.chainClass[j];
-        P.todoSorted[pixBase[cr & 31u] + (cr >> 5)] = j;
+        P.todoSorted[pixBase[cr & ((1u << kClassBits) - 1u)] + (cr >> kClassBits)] = j;
     }
 }
 
