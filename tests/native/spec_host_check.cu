@@ -40,8 +40,8 @@ int main() {
     unsigned int prev = 0;
     for (int c = 0; c < spec::kClasses; c++) {
         const unsigned int K = spec::classK(c);
-        if (K <= prev || K % 4u != 0u) { std::printf("class %d: %u after %u\n", c, K, prev); return 1; }
-        if (c > 0 && 2u * K > 3u * prev) { std::printf("class %d grows by more than 1.5x\n", c); return 1; }
+        if (K <= prev || K % 2u != 0u) { std::printf("class %d: %u after %u\n", c, K, prev); return 1; }
+        if (c > 0 && 4u * K > 5u * prev) { std::printf("class %d grows by more than 1.25x\n", c); return 1; }
         prev = K;
     }
     if (spec::classK(0) != 8u || prev < (unsigned int)spec::kMaxK / 2u) { std::printf("class range\n"); return 1; }
