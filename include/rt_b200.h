@@ -205,6 +205,23 @@ int rt_peer_is_open(rt_ctx* ctx);
 /* Order the stream behind any asynchronous read-back of the target the next pass will write. */
 int rt_target_wait_reads(rt_ctx* ctx);
 
+/* One draw without any allocation.  No counterpart in the reference: added for
+ * callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * Renders the tile (tileX, tileY) of frame frameNumber of the uploaded scene with the uniforms of rt_set_params, like
+ * rt_render_pass, but into buffers the CALLER passes: prev_dev / next_dev are width x height RGBA32F device buffers
+ * (row 0 = bottom row), prev_dev is read when frameNumber > 0 or the tile does not cover the frame (pixels outside the
+ * tile are copied from it) and may be NULL otherwise; the context's own targets and accum_index are not touched.  It
+ * runs the wavefront variant (primary stage -> queue of hit pixels -> path stage) with the queue in a static device
+ * array of RT_STATIC_MAX_PIXELS x 36 bytes + 256 (36 MiB, held by every GPU that loads the library until exit), so
+ * neither this call nor anything it calls allocates or frees memory.  A tile that owns more than RT_STATIC_MAX_PIXELS
+ * pixels, or a frame wider or higher than 65535, is refused with RT_ERR_INVALID.  All calls, from every context of the
+ * process on that GPU, share the array: it keeps the last call's contents (the call clears the counters it needs at
+ * zero), and calls that overlap on the GPU — two streams, two contexts — race; order them.  Results are bit-identical
+ * to rt_render_pass. */
+#define RT_STATIC_MAX_PIXELS (1 << 20)
+int rt_render_pass_static(rt_ctx* ctx, int frameNumber, int tileX, int tileY, int width, int height,
+                          const void* prev_dev, void* next_dev);
+
 /* sum target -> mean RGBA32F in place: target = target * (1 / n_frames) is NOT what the reference
  * does; it divides.  Used after the frame-sharded reduce. */
 int rt_finish_sum(rt_ctx* ctx, int total_frames);

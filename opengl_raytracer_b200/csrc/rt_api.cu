@@ -24,6 +24,7 @@ cudaError_t rtLaunchPixel(const PassParams& P, bool count, bool ids, cudaStream_
 cudaError_t rtLaunchPersistent(const PassParams& P, bool count, bool ids, int sms, cudaStream_t stream);
 cudaError_t rtLaunchPool(const PassParams& P, bool count, bool ids, int sms, cudaStream_t stream);
 cudaError_t rtLaunchWavefront(const PassParams& P, bool count, bool ids, int sms, cudaStream_t stream);
+cudaError_t rtLaunchWavefrontStatic(const PassParams& P, int device, int sms, cudaStream_t stream);
 cudaError_t rtLaunchSamples(const PassParams& P, bool ids, int sms, uint32_t* todoA, uint32_t* todoB, cudaStream_t stream);
 cudaError_t rtLaunchChain(const PassParams& P, bool ids, int sms, cudaStream_t stream);
 size_t rtChainRingBytes(int sms);
@@ -934,6 +935,47 @@ static int bandCopy(rt_ctx* c, int tileY, void* dense, int toDense) {
 
 int rt_band_gather(rt_ctx* c, int tileY, void* dense) { return bandCopy(c, tileY, dense, 1); }
 int rt_band_scatter(rt_ctx* c, int tileY, const void* dense) { return bandCopy(c, tileY, const_cast<void*>(dense), 0); }
+
+// One draw into caller-provided buffers with no allocation anywhere on the path (include/rt_b200.h).
+int rt_render_pass_static(rt_ctx* c, int frameNumber, int tileX, int tileY, int width, int height, const void* prevDev,
+                          void* nextDev) {
+    if (!c) return RT_ERR_INVALID;
+    if (!c->haveScene) return fail(c, RT_ERR_STATE, "rt_render_pass_static before rt_scene_upload");
+    if (!c->haveParams) return fail(c, RT_ERR_STATE, "rt_render_pass_static before rt_set_params");
+    if (width <= 0 || height <= 0 || width > 65535 || height > 65535)
+        return fail(c, RT_ERR_INVALID, "rt_render_pass_static: frame %d x %d (1 .. 65535 each way)", width, height);
+    if (!nextDev) return fail(c, RT_ERR_INVALID, "rt_render_pass_static: no output buffer");
+    const rt_params& u = c->params;
+    PassParams P{};
+    P.scene = c->scene;
+    P.tileX = tileX; P.tileY = tileY; P.tileSizeX = u.tileSizeX; P.tileSizeY = u.tileSizeY;
+    P.numTilesX = u.numTilesX; P.numTilesY = u.numTilesY;
+    P.lambertian = u.lambertian; P.nBounces = u.nBounces; P.raysPerPixel = u.rays_per_pixel; P.frameNumber = frameNumber;
+    P.skyBrightness = u.skyBrightness; P.xStep = u.xStep; P.yStep = u.yStep; P.dirStartX = u.dirStartX;
+    P.dirStartY = u.dirStartY; P.jitterAmount = u.jitterAmount;
+    for (int k = 0; k < 3; k++) {
+        P.camPos[k] = u.camPos[k]; P.camRight[k] = u.camRight[k]; P.camUp[k] = u.camUp[k]; P.camForward[k] = u.camForward[k];
+    }
+    P.width = width; P.height = height;
+    P.prev = static_cast<const float4*>(prevDev); P.next = static_cast<float4*>(nextDev);
+    P.ownedW = ownedCount(width, u.tileSizeX, u.numTilesX, tileX);
+    P.ownedH = ownedCount(height, u.tileSizeY, u.numTilesY, tileY);
+    P.sumMode = 0;
+    const long long owned = (long long)P.ownedW * P.ownedH;
+    if (owned > (long long)RT_STATIC_MAX_PIXELS)
+        return fail(c, RT_ERR_INVALID, "rt_render_pass_static: the tile owns %lld pixels, the static queue holds %d "
+                    "(RT_STATIC_MAX_PIXELS); draw smaller tiles or use rt_render_pass", owned, int(RT_STATIC_MAX_PIXELS));
+    const bool covers = P.ownedW == width && P.ownedH == height;
+    if (!prevDev && (frameNumber > 0 || !covers))
+        return fail(c, RT_ERR_INVALID, "rt_render_pass_static: the previous frame is read (frameNumber > 0 or a partial tile) but prev_dev is NULL");
+    Bind bind(c);
+    if (!covers)    // pixels outside the tile keep the previous target's texel, all four channels (fragment.glsl:382-386)
+        RT_CUDA(c, cudaMemcpyAsync(nextDev, prevDev, size_t(width) * height * sizeof(float4), cudaMemcpyDeviceToDevice, c->stream));
+    const cudaError_t e = rtLaunchWavefrontStatic(P, c->device, c->smCount, c->stream);
+    if (e != cudaSuccess) return fail(c, RT_ERR_CUDA, "rt_render_pass_static: %s", cudaGetErrorString(e));
+    cudaEventRecord(c->sets[c->curSet].lastUse, c->stream);     // the next upload into this set waits for it
+    return RT_OK;
+}
 
 int rt_peer_export(rt_ctx* c, void* handlesOut) {
     if (!c || !handlesOut) return RT_ERR_INVALID;

@@ -10,6 +10,7 @@
 #include <algorithm>
 #include <cstdio>
 #include <cstdlib>
+#include <mutex>
 
 #include "../../include/rt_b200.h"
 #include "rt_shade.cuh"
@@ -381,6 +382,70 @@ cudaError_t rtSpecInit() {
     cudaError_t e = cudaMemcpyToSymbol(spec::cJumpLo, lo, sizeof lo);
     if (e != cudaSuccess) return e;
     return cudaMemcpyToSymbol(spec::cJumpHi, hi, sizeof hi);
+}
+
+// ---- WAVEFRONT pass without allocation (rt_render_pass_static): the queue and both counters live in a file-scope
+// array instead of cudaMalloc'ed buffers.  Every GPU that loads the library holds the array until exit.  All calls share
+// it: a call clears the counters it needs at zero on its stream, and calls that overlap on the GPU race.
+namespace {
+constexpr size_t kStaticMaxPixels = RT_STATIC_MAX_PIXELS;
+constexpr size_t kStaticHeaderBytes = 256;              // [0] queue count, [1] work counter
+constexpr size_t kStaticBytes = kStaticHeaderBytes + kStaticMaxPixels * (sizeof(float4) + sizeof(float4) + sizeof(uint32_t));
+}  // namespace
+static __device__ __align__(256) unsigned char gStaticScratch[kStaticBytes];
+
+namespace {
+constexpr int kStaticMaxDevices = 64;
+std::mutex gStaticLock;
+unsigned char* gStaticAddress[kStaticMaxDevices] = {};
+}  // namespace
+
+// The array's device address on `device`, which must be current.  In host code `gStaticScratch` is only a stand-in for
+// the symbol, never a device pointer: the address comes from cudaGetSymbolAddress, once per device.
+static cudaError_t staticScratchAddress(int device, unsigned char** out) {
+    if (device < 0 || device >= kStaticMaxDevices) return cudaErrorInvalidDevice;
+    std::lock_guard<std::mutex> guard(gStaticLock);
+    if (gStaticAddress[device] == nullptr) {
+        void* p = nullptr;
+        const cudaError_t e = cudaGetSymbolAddress(&p, gStaticScratch);
+        if (e != cudaSuccess) return e;
+        gStaticAddress[device] = static_cast<unsigned char*>(p);
+    }
+    *out = gStaticAddress[device];
+    return cudaSuccess;
+}
+
+cudaError_t rtLaunchWavefrontStatic(const PassParams& Pin, int device, int sms, cudaStream_t stream) {
+    PassParams P = Pin;
+    if (P.ownedW <= 0 || P.ownedH <= 0) return cudaSuccess;
+    if ((unsigned long long)P.ownedW * (unsigned long long)P.ownedH > kStaticMaxPixels) return cudaErrorInvalidValue;
+    unsigned char* base = nullptr;
+    cudaError_t e = staticScratchAddress(device, &base);
+    if (e != cudaSuccess) return e;
+    P.queueCount = reinterpret_cast<unsigned int*>(base);
+    P.workCounter = reinterpret_cast<unsigned int*>(base) + 1;
+    P.queueA = reinterpret_cast<float4*>(base + kStaticHeaderBytes);
+    P.queueB = P.queueA + kStaticMaxPixels;
+    P.queuePix = reinterpret_cast<uint32_t*>(P.queueB + kStaticMaxPixels);
+    P.queueWork = nullptr;                                  // counting passes only
+    P.counters = nullptr; P.primaryIds = nullptr;
+    if ((e = cudaMemsetAsync(base, 0, kStaticHeaderBytes, stream)) != cudaSuccess) return e;   // the last call's counts
+    const size_t smem = wave::smemBytes(P.scene.stackDepth);
+    dim3 grid((P.ownedW + 15) / 16, (P.ownedH + 7) / 8);
+    if (smem > 48 * 1024) {
+        cudaFuncSetAttribute(wave::rtPrimaryKernel<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem));
+        cudaFuncSetAttribute(wave::rtPathKernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem));
+    }
+    wave::rtPrimaryKernel<false, false><<<grid, wave::kThreads, smem, stream>>>(P);
+    if ((e = cudaGetLastError()) != cudaSuccess) return e;
+    if (P.nBounces <= 0 || P.raysPerPixel <= 0) return cudaSuccess;   // nothing was queued
+    int perSm = 0;
+    if ((e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSm, wave::rtPathKernel<false>, wave::kThreads, smem)) != cudaSuccess) return e;
+    if (perSm < 1) perSm = 1;
+    const long long pixels = (long long)P.ownedW * P.ownedH;
+    const long long want = (pixels + wave::kThreads - 1) / wave::kThreads;
+    wave::rtPathKernel<false><<<int(std::min<long long>((long long)sms * perSm, std::max<long long>(want, 1))), wave::kThreads, smem, stream>>>(P);
+    return cudaGetLastError();
 }
 
 // kernel launches of one samples pass that uses tables: stage 1 + round 0 (evaluate, chain) + 3 per later round

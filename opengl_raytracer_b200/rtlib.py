@@ -56,6 +56,7 @@ COUNTER_NAMES = ("rays", "rays_traced", "internal", "leaves", "tri_tests", "hits
 VARIANTS = {"auto": 0, "pixel": 1, "persistent": 2, "wavefront": 3, "pool": 4, "samples": 5, "chain": 6}
 PASS_COUNTERS, PASS_PRIMARY_IDS, PASS_SKIP_MASKED, PASS_TO_PEER = 1, 2, 4, 8
 IPC_HANDLE_BYTES = 64
+STATIC_MAX_PIXELS = 1 << 20
 SUM_CONTINUE = 1
 
 _lib = None
@@ -110,6 +111,7 @@ def load_library(path: str | None = None):
         "rt_band_rows": (i, [vp, i]),
         "rt_band_gather": (i, [vp, i, vp]),
         "rt_band_scatter": (i, [vp, i, vp]),
+        "rt_render_pass_static": (i, [vp, i, i, i, i, i, vp, vp]),
         "rt_peer_export": (i, [vp, vp]),
         "rt_peer_open": (i, [vp, vp]),
         "rt_peer_close": (i, [vp]),
@@ -248,6 +250,13 @@ class Context:
     # -- draw (main.py:376-394)
     def render_pass(self, frameNumber: int, tileX: int = 0, tileY: int = 0, flags: int = 0):
         self._check(self.lib.rt_render_pass_ex(self.handle, frameNumber, tileX, tileY, flags))
+
+    def render_pass_static(self, frameNumber: int, tileX: int, tileY: int, width: int, height: int, prev_dev_ptr, next_dev_ptr: int):
+        """One draw into caller-provided RGBA32F device buffers without any allocation (``rt_render_pass_static``: the
+        wavefront queue lives in a static device array of ``STATIC_MAX_PIXELS`` entries shared by all calls on the GPU —
+        calls that overlap on the GPU race).  ``prev_dev_ptr`` may be None for frame 0 of a tile that covers the frame."""
+        self._check(self.lib.rt_render_pass_static(self.handle, frameNumber, tileX, tileY, width, height,
+                                                   ctypes.c_void_p(prev_dev_ptr or None), ctypes.c_void_p(next_dev_ptr)))
 
     def render_frames(self, first_frame: int, n_frames: int):
         self._check(self.lib.rt_render_frames(self.handle, first_frame, n_frames))
