@@ -20,9 +20,10 @@
 //               from a global counter with one warp-aggregated atomic).
 // SHADE, LEAF and DEEP run when RT_POOL_TS / RT_POOL_TL / RT_POOL_TD lanes have a ray waiting for them (checked in
 // that order), or when nothing else can run.  Measured outcome: profiles/r01_variants.md §5 — not what AUTO picks.
-// The first `topCount` nodes of the tree (breadth-first numbering, so: its top levels — 78-89 % of all node
-// visits with 512-1024 nodes, tools/node_hist.py) are staged in shared memory, where a divergent 16-byte read
-// costs bank conflicts instead of one L1 wavefront per lane.
+// The first `topCount` nodes of the tree (under breadth-first numbering, RT_NODE_ORDER=bfs, which this variant was built
+// and measured with: its top levels — 78-89 % of all node visits with 512-1024 nodes, tools/node_hist.py) are staged in
+// shared memory, where a divergent 16-byte read costs bank conflicts instead of one L1 wavefront per lane.  (Since round 2
+// the default numbering is depth-first: the staged prefix is then the root's leftmost subtree — correct, less useful.)
 //
 // Per-ray semantics are exactly those of traverse()/pixelFrame() (rt_device.cuh / rt_kernels.cu): the visiting
 // order inside a ray never changes, only which ray a lane advances when.
@@ -174,7 +175,8 @@ __global__ void __launch_bounds__(T, 1) rtPoolKernel(const __grid_constant__ Pas
     const Smem<T, K> sm(poolSmem, sc.stackDepth, topCount);
     constexpr uint32_t STRIDE = K * T;
 
-    // stage the top of the tree (nodes are numbered breadth-first)
+    // stage the first nodes of the array (its top levels under RT_NODE_ORDER=bfs, the numbering this variant was built
+    // for; with the default depth-first numbering: the root and the leftmost subtree — still correct, less useful)
     for (int i = tid; i < topCount * 3; i += T) {
         const int node = i / 3, part = i - node * 3;
         sm.top[part * topCount + node] = __ldg(reinterpret_cast<const float4*>(sc.nodes + node) + part);
