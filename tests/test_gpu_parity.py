@@ -535,3 +535,22 @@ def test_chain_rings_are_never_read_before_they_are_cleared(ctx, oracle_mod, sce
     got = _render_gpu(ctx, tris, boxes, indices, params, 2, "chain")
     want = oracle_mod.render_frames(tris, boxes, indices, params, 0, 2)
     assert got.tobytes() == want.tobytes(), f"{(got != want).any(-1).sum()} pixels differ"
+
+
+@pytest.mark.parametrize("variant", ["auto", "pool", "chain"])
+def test_node_numbering_does_not_change_results(ctx, oracle_mod, scene_buffers, monkeypatch, variant):
+    """rt_scene_upload numbers the internal nodes depth-first (subtrees contiguous); RT_NODE_ORDER=bfs keeps round 1's
+    breadth-first numbering.  Only addresses change: image, primary ids and the work counters are the oracle's either way
+    (POOL stages the first nodes of the array in shared memory, whichever they are)."""
+    tris, boxes, indices, cfg = scene_buffers("cfg4_open")
+    params = cfg.scaled(160, 90, 6).params()
+    want, want_ids, want_cnt = oracle_mod.render_pass(tris, boxes, indices, params, want_ids=True, want_counters=True)
+    flags = rtlib.PASS_PRIMARY_IDS | (0 if variant == "chain" else rtlib.PASS_COUNTERS)
+    for order in ("dfs", "bfs"):
+        monkeypatch.setenv("RT_NODE_ORDER", order)
+        got = _render_gpu(ctx, tris, boxes, indices, params, 1, variant, flags=flags)
+        assert got.tobytes() == want.tobytes(), order
+        assert np.array_equal(ctx.read_primary_ids(), want_ids), order
+        if variant != "chain":
+            cnt = ctx.read_counters()
+            assert {k: cnt[k] for k in EXACT_COUNTERS} == {k: want_cnt[k] for k in EXACT_COUNTERS}, order
