@@ -217,7 +217,8 @@ int rt_target_wait_reads(rt_ctx* ctx);
  * pixels, or a frame wider or higher than 65535, is refused with RT_ERR_INVALID.  All calls, from every context of the
  * process on that GPU, share the array: it keeps the last call's contents (the call clears the counters it needs at
  * zero), and calls that overlap on the GPU — two streams, two contexts — race; order them.  Results are bit-identical
- * to rt_render_pass. */
+ * to rt_render_pass.  The first call on a device resolves the array's address (cudaGetSymbolAddress) and loads the two
+ * kernels: make one call before entering a region where even that is unwelcome (graph capture). */
 #define RT_STATIC_MAX_PIXELS (1 << 20)
 int rt_render_pass_static(rt_ctx* ctx, int frameNumber, int tileX, int tileY, int width, int height,
                           const void* prev_dev, void* next_dev);
