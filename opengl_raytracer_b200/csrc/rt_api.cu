@@ -264,6 +264,14 @@ void freeTargets(rt_ctx* c) {
 }
 
 // How many coordinates c in [0, extent) satisfy (c / tileSize) % numTiles == tile.
+// Whether triangleTest defers the fetch of a triangle's edges (rt_device.cuh): yes when the pass is large enough to keep
+// the L1 data pipe busy (8 Mi pixel-samples: a 4K frame at 1 spp, 1080p at 4), no for small, latency-bound passes.
+// Measured on B200 (profiles/r02_variants.md section 10); RT_DEFER_EDGES=0/1 overrides.
+int deferEdgesFor(long long ownedPixels, int raysPerPixel) {
+    if (const char* e = getenv("RT_DEFER_EDGES")) return atoi(e) != 0;
+    return ownedPixels * std::max(raysPerPixel, 1) >= (8ll << 20) ? 1 : 0;
+}
+
 int ownedCount(int extent, int tileSize, int numTiles, int tile) {
     if (tileSize <= 0 || numTiles <= 0 || tile < 0 || tile >= numTiles) return 0;
     const long long period = (long long)tileSize * numTiles;
@@ -663,6 +671,7 @@ int renderPass(rt_ctx* c, int frameNumber, int tileX, int tileY, int flags, int 
     P.ownedH = ownedCount(c->height, u.tileSizeY, u.numTilesY, tileY);
     P.sumMode = sumMode;
     P.workCounter = c->dWork;
+    P.scene.deferEdges = deferEdgesFor((long long)P.ownedW * P.ownedH, u.rays_per_pixel);
     const bool covers = P.ownedW == c->width && P.ownedH == c->height;
     if (!covers && !(flags & RT_PASS_SKIP_MASKED)) {
         // pixels outside the tile keep the previous target's texel, all four channels (fragment.glsl:382-386)
@@ -987,6 +996,7 @@ int rt_render_pass_static(rt_ctx* c, int frameNumber, int tileX, int tileY, int 
     P.ownedH = ownedCount(height, u.tileSizeY, u.numTilesY, tileY);
     P.sumMode = 0;
     const long long owned = (long long)P.ownedW * P.ownedH;
+    P.scene.deferEdges = deferEdgesFor(owned, u.rays_per_pixel);
     if (owned > (long long)RT_STATIC_MAX_PIXELS)
         return fail(c, RT_ERR_INVALID, "rt_render_pass_static: the tile owns %lld pixels, the static queue holds %d "
                     "(RT_STATIC_MAX_PIXELS); draw smaller tiles or use rt_render_pass", owned, int(RT_STATIC_MAX_PIXELS));

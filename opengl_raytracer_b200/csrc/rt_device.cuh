@@ -60,10 +60,16 @@ RT_DEV void loadNode(const NodeRec* node, float4& q0, float4& q1, float4& q2, in
     refs = make_int2(__float_as_int(q3.x), __float_as_int(q3.y));
 }
 // One TriRec: v0 | eAB | eAC | N in q0..q2 (the padding half-line rides along with q2).
-RT_DEV void loadTri(const TriRec* rec, float4& q0, float4& q1, float4& q2) {
-    float4 pad;
-    ld256(rec, q0, q1);
-    ld256(reinterpret_cast<const char*>(rec) + 32, q2, pad);
+// TriRec in two halves (rt_types.h): the plane (v0, N) first, the edges when they are needed.
+RT_DEV void loadTriPlane(const TriRec* rec, f3& v0, f3& N) {
+    float4 a, b;
+    ld256(rec, a, b);
+    v0 = mk3(a.x, a.y, a.z); N = mk3(a.w, b.x, b.y);
+}
+RT_DEV void loadTriEdges(const TriRec* rec, f3& eAB, f3& eAC) {
+    float4 a, b;
+    ld256(reinterpret_cast<const char*>(rec) + 32, a, b);
+    eAB = mk3(a.x, a.y, a.z); eAC = mk3(a.w, b.x, b.y);
 }
 
 // fragment.glsl:206-218.  float(result)/2^32*2-1: the scalings are exact, so one rounding at the -1.
@@ -113,13 +119,18 @@ struct StackRef {
 // returns are folded into one predicate; each comparison is the shader's own (NaN-faithful): reject when
 // abs(det) < EPS, t <= EPS, u < 0, v < 0 or u + v > 1.  Values computed past a rejected test are unused
 // (1/det of a tiny det may be inf/NaN — harmless, the predicate is already false).
+// DEFER: fetch the edges only in the lanes whose hit distance is in range — one L1 wavefront less per rejected candidate,
+// one more dependent memory access for the accepted ones.  It pays where the data pipe is the ceiling (closed room 4K 8 spp
+// 154.2 -> 149.8 ms) and costs where latency is (small frames: cfg2_open 1.46 -> 1.62 ms; the speculating variants), so
+// the pass decides on the host (DeviceScene::deferEdges, rt_api.cu) between two instantiations of the pixel and persistent
+// kernels; everything else does not defer.  (A run-time flag instead of the template was measured: slower than either.)
+template <bool DEFER>
 RT_DEV bool triangleTest(const TriRec* __restrict__ rec, f3 o, f3 d, float closestT, float& tOut, float& uOut,
                          float& vOut) {
-    float4 q0, q1, q2;
-    loadTri(rec, q0, q1, q2);
     const float EPS = 1e-6f;
-    const f3 v0 = mk3(q0.x, q0.y, q0.z), eAB = mk3(q0.w, q1.x, q1.y), eAC = mk3(q1.z, q1.w, q2.x);
-    const f3 N = mk3(q2.y, q2.z, q2.w);
+    f3 v0, N, eAB, eAC;
+    loadTriPlane(rec, v0, N);
+    if (!DEFER) loadTriEdges(rec, eAB, eAC);
     const float det = dot3(d, N);
     bool ok = !(fabsf(det) < EPS);
     const float invDet = __frcp_rn(det);
@@ -127,6 +138,7 @@ RT_DEV bool triangleTest(const TriRec* __restrict__ rec, f3 o, f3 d, float close
     const float t = mul(-dot3(ao, N), invDet);
     ok = ok && !(t <= EPS) && (t < closestT && t > 1e-6f);
     if (ok) {
+        if (DEFER) loadTriEdges(rec, eAB, eAC);
         const f3 dao = cross3(ao, d);
         const float u = mul(-dot3(eAC, dao), invDet);
         const float v = mul(dot3(eAB, dao), invDet);
@@ -147,7 +159,7 @@ RT_DEV bool triangleTest(const TriRec* __restrict__ rec, f3 o, f3 d, float close
 // scheduling the lanes of a warp reconverge at the immediate post-dominator of each branch, and an early
 // `return` inside the loop moves that point to the function exit — the first version did that and ran with
 // 2 of 32 lanes active (profiles/r01_ncu_notes.md).
-template <bool COUNT>
+template <bool COUNT, bool DEFER = false>
 RT_DEV RayHit traverse(const DeviceScene& sc, f3 o, f3 d, StackRef st, WorkCount& wc) {
     RayHit best;
     best.t = 1e30f; best.u = 0.f; best.v = 0.f; best.slot = -1;
@@ -201,7 +213,7 @@ RT_DEV RayHit traverse(const DeviceScene& sc, f3 o, f3 d, StackRef st, WorkCount
             if (COUNT) { wc.leaves++; wc.tris += count; }
             for (uint32_t k = 0; k < count; k++) {
                 float t, u, v;
-                if (triangleTest(sc.tris + first + k, o, d, best.t, t, u, v)) {
+                if (triangleTest<DEFER>(sc.tris + first + k, o, d, best.t, t, u, v)) {
                     best.t = t; best.u = u; best.v = v; best.slot = int32_t(first + k);
                 }
             }

@@ -29,7 +29,7 @@ struct PathCounters {
 };
 
 // One pixel-frame: fragment.glsl main() from :388 on.  Returns the pixel's colour for this frame.
-template <bool COUNT, bool IDS>
+template <bool COUNT, bool IDS, bool DEFER>
 RT_DEV f3 pixelFrame(const PassParams& P, int px, int py, StackRef st, PathCounters& pc, int32_t& primaryId) {
     const DeviceScene& sc = P.scene;
     uint32_t seed;
@@ -43,7 +43,7 @@ RT_DEV f3 pixelFrame(const PassParams& P, int px, int py, StackRef st, PathCount
     RayHit primaryHit;
     primaryHit.slot = -1; primaryHit.t = 0.f; primaryHit.u = 0.f; primaryHit.v = 0.f;
     if (P.nBounces > 0 && P.raysPerPixel > 0) {
-        primaryHit = traverse<COUNT>(sc, camPos, primaryDir, st, primaryWork);
+        primaryHit = traverse<COUNT, DEFER>(sc, camPos, primaryDir, st, primaryWork);
         if (COUNT) pc.v[RT_CNT_RAYS_TRACED]++;
     }
     if (IDS) primaryId = primaryHit.slot >= 0 ? int32_t(__ldg(sc.triId + primaryHit.slot)) : -1;
@@ -64,7 +64,7 @@ RT_DEV f3 pixelFrame(const PassParams& P, int px, int py, StackRef st, PathCount
                 }
             } else {
                 WorkCount wc = {0, 0, 0, 0};
-                h = traverse<COUNT>(sc, o, d, st, wc);
+                h = traverse<COUNT, DEFER>(sc, o, d, st, wc);
                 if (COUNT) {
                     pc.v[RT_CNT_RAYS_TRACED]++;
                     pc.v[RT_CNT_INTERNAL] += wc.internal; pc.v[RT_CNT_LEAVES] += wc.leaves;
@@ -107,7 +107,7 @@ RT_DEV void flushCounters(const PassParams& P, PathCounters& pc) {
     }
 }
 
-template <bool COUNT, bool IDS>
+template <bool COUNT, bool IDS, bool DEFER = false>      // DEFER: see triangleTest (rt_device.cuh)
 __global__ void __launch_bounds__(kBlockThreads) rtPixelKernel(const __grid_constant__ PassParams P) {
     extern __shared__ uint2 stackMem[];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -123,7 +123,7 @@ __global__ void __launch_bounds__(kBlockThreads) rtPixelKernel(const __grid_cons
         StackRef st;
         st.base = stackMem; st.stride = kBlockThreads;
         int32_t primaryId = -1;
-        const f3 curr = pixelFrame<COUNT, IDS>(P, px, py, st, pc, primaryId);
+        const f3 curr = pixelFrame<COUNT, IDS, DEFER>(P, px, py, st, pc, primaryId);
         const size_t at = size_t(py) * size_t(P.width) + size_t(px);
         storePixel(P, at, accumulate(P, curr, at));
         if (IDS) P.primaryIds[at] = primaryId;
@@ -200,10 +200,10 @@ __global__ void rtBuildRecordsKernel(const float4* __restrict__ raw, const uint3
         const float ny = __fsub_rn(__fmul_rn(abz, acx), __fmul_rn(acz, abx));
         const float nz = __fsub_rn(__fmul_rn(abx, acy), __fmul_rn(acx, aby));
         float4* t = reinterpret_cast<float4*>(tris + slot);
-        t[0] = make_float4(v0.x, v0.y, v0.z, abx);
-        t[1] = make_float4(aby, abz, acx, acy);
-        t[2] = make_float4(acz, nx, ny, nz);
-        t[3] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+        t[0] = make_float4(v0.x, v0.y, v0.z, nx);
+        t[1] = make_float4(ny, nz, 0.0f, 0.0f);
+        t[2] = make_float4(abx, aby, abz, acx);
+        t[3] = make_float4(acy, acz, 0.0f, 0.0f);
         float4* s = reinterpret_cast<float4*>(shade + slot);
         s[0] = make_float4(n0.x, n0.y, n0.z, n1.x);
         s[1] = make_float4(n1.y, n1.z, n2.x, n2.y);
@@ -231,7 +231,12 @@ cudaError_t rtLaunchPixel(const PassParams& P, bool count, bool ids, cudaStream_
             cudaFuncSetAttribute(rtPixelKernel<C, I>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)); \
         rtPixelKernel<C, I><<<grid, kBlockThreads, smem, stream>>>(P);                                   \
     } while (0)
-    if (count && ids) RT_LAUNCH(true, true);
+    // the deferring instantiation (triangleTest) exists for the plain pass only; counting / id passes are not timed
+    if (!count && !ids && P.scene.deferEdges) {
+        if (smem > 48 * 1024)
+            cudaFuncSetAttribute(rtPixelKernel<false, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem));
+        rtPixelKernel<false, false, true><<<grid, kBlockThreads, smem, stream>>>(P);
+    } else if (count && ids) RT_LAUNCH(true, true);
     else if (count) RT_LAUNCH(true, false);
     else if (ids) RT_LAUNCH(false, true);
     else RT_LAUNCH(false, false);
@@ -250,21 +255,23 @@ cudaError_t rtLaunchPersistent(const PassParams& Pin, bool count, bool ids, int 
     // no more CTAs than there is work for: one warp per 32 pixel indices
     const long long tiles = (long long)((P.ownedW + 7) / 8) * ((P.ownedH + 3) / 4);
     const int needed = int(std::min<long long>((tiles * 32 + vote::kThreads - 1) / vote::kThreads, 1 << 30));
-#define RT_LAUNCH(C, I)                                                                                          \
+#define RT_LAUNCH(C, I, D)                                                                                       \
     do {                                                                                                         \
         if (smem > 48 * 1024)                                                                                    \
-            cudaFuncSetAttribute(vote::rtVoteKernel<C, I>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)); \
+            cudaFuncSetAttribute(vote::rtVoteKernel<C, I, D>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)); \
         int perSm = 0;                                                                                           \
-        e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSm, vote::rtVoteKernel<C, I>, vote::kThreads, smem); \
+        e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSm, vote::rtVoteKernel<C, I, D>, vote::kThreads, smem); \
         if (e != cudaSuccess) return e;                                                                          \
         if (perSm < 1) perSm = 1;                                                                                \
         if (const char* v = getenv("RT_VOTE_CTAS")) perSm = std::max(1, std::min(perSm, atoi(v)));                \
-        vote::rtVoteKernel<C, I><<<std::min(sms * perSm, std::max(needed, 1)), vote::kThreads, smem, stream>>>(P); \
+        vote::rtVoteKernel<C, I, D><<<std::min(sms * perSm, std::max(needed, 1)), vote::kThreads, smem, stream>>>(P); \
     } while (0)
-    if (count && ids) RT_LAUNCH(true, true);
-    else if (count) RT_LAUNCH(true, false);
-    else if (ids) RT_LAUNCH(false, true);
-    else RT_LAUNCH(false, false);
+    // the deferring instantiation (triangleTest) exists for the plain pass only; counting / id passes are not timed
+    if (!count && !ids && P.scene.deferEdges) RT_LAUNCH(false, false, true);
+    else if (count && ids) RT_LAUNCH(true, true, false);
+    else if (count) RT_LAUNCH(true, false, false);
+    else if (ids) RT_LAUNCH(false, true, false);
+    else RT_LAUNCH(false, false, false);
 #undef RT_LAUNCH
     return cudaGetLastError();
 }

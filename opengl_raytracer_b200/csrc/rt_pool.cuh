@@ -331,7 +331,7 @@ __global__ void __launch_bounds__(T, 1) rtPoolKernel(const __grid_constant__ Pas
                 float bestU = 0.f, bestV = 0.f;
                 for (uint32_t k = 0; k < count; k++) {
                     float t, u, v;
-                    if (triangleTest(sc.tris + first + k, o, d, bestT, t, u, v)) {
+                    if (triangleTest<false>(sc.tris + first + k, o, d, bestT, t, u, v)) {
                         bestT = t; bestU = u; bestV = v; bestSlot = int32_t(first + k);
                     }
                 }

@@ -22,8 +22,9 @@ RT_DEV SurfaceHit resolveHit(const DeviceScene& sc, const RayHit& h, f3 o, f3 d)
     const f3 n0 = mk3(s0.x, s0.y, s0.z), n1 = mk3(s0.w, s1.x, s1.y), n2 = mk3(s1.z, s1.w, s2.x);
     f3 n = normalize3(add3(add3(scale3(n0, w), scale3(n1, h.u)), scale3(n2, h.v)));
     if (length3(n) < 1e-6f) {
-        const float4 q2 = __ldg(reinterpret_cast<const float4*>(sc.tris + h.slot) + 2);
-        n = normalize3(mk3(q2.y, q2.z, q2.w));
+        const float4 t0 = __ldg(reinterpret_cast<const float4*>(sc.tris + h.slot));
+        const float4 t1 = __ldg(reinterpret_cast<const float4*>(sc.tris + h.slot) + 1);
+        n = normalize3(mk3(t0.w, t1.x, t1.y));
     }
     if (dot3(d, n) > 0.0f) n = neg3(n);
     r.normal = n;

@@ -345,7 +345,7 @@ __global__ void __launch_bounds__(kThreads) rtSpecEvalKernel(const __grid_consta
                 }
             }
         } else if (__popc(mL) >= leafT || mI == 0u) {
-            if (L.mode == MODE_LEAF) stepLeaf<false>(sc, L, stack, stride, cnt);
+            if (L.mode == MODE_LEAF) stepLeaf<false, false>(sc, L, stack, stride, cnt);
         } else {
 #pragma unroll 1
             for (int s = 0; s < kBurst; s++)

@@ -41,10 +41,12 @@ struct alignas(32) NodeRec {
 };
 
 struct alignas(32) TriRec {
-    float v0x, v0y, v0z, abx;
-    float aby, abz, acx, acy;
-    float acz, nx, ny, nz;
-    float pad[4];
+    // first 32 bytes: what the distance test needs (plane: v0 and N); second 32 bytes: the edges, fetched only by the
+    // lanes whose hit distance is in range (rt_device.cuh triangleTest) — one L1 wavefront less for the others
+    float v0x, v0y, v0z, nx;
+    float ny, nz, pad0, pad1;
+    float abx, aby, abz, acx;
+    float acy, acz, pad2, pad3;
 };
 
 struct alignas(32) ShadeRec {
@@ -66,6 +68,7 @@ struct DeviceScene {
     int32_t rootRef;
     int32_t stackDepth;             // entries a traversal can need (tree depth + 1)
     uint32_t nNodes, nSlots;
+    int32_t deferEdges;             // per pass: triangleTest fetches a triangle's edges only where the distance test passed
 };
 
 // Everything a pass needs, passed by value as a __grid_constant__ kernel parameter.

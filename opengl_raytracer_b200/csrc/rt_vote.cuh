@@ -122,7 +122,7 @@ RT_DEV void stepInternal(const DeviceScene& sc, Lane& L, uint2* stack, uint32_t 
 }
 
 // One leaf (fragment.glsl:266-279): every triangle in slot order, first found wins ties; then pop.
-template <bool COUNT>
+template <bool COUNT, bool DEFER = false>      // DEFER: see triangleTest (rt_device.cuh)
 RT_DEV void stepLeaf(const DeviceScene& sc, Lane& L, const uint2* stack, uint32_t stride, uint32_t* cnt) {
     const uint32_t code = uint32_t(~L.cur);
     uint32_t count = code & ((1u << RT_LEAF_BITS) - 1u);
@@ -134,7 +134,7 @@ RT_DEV void stepLeaf(const DeviceScene& sc, Lane& L, const uint2* stack, uint32_
     if (COUNT) { cnt[RT_CNT_LEAVES]++; cnt[RT_CNT_TRI_TESTS] += count; }
     for (uint32_t k = 0; k < count; k++) {
         float t, u, v;
-        if (triangleTest(sc.tris + first + k, L.o, L.d, L.best.t, t, u, v)) {
+        if (triangleTest<DEFER>(sc.tris + first + k, L.o, L.d, L.best.t, t, u, v)) {
             L.best.t = t; L.best.u = u; L.best.v = v; L.best.slot = int32_t(first + k);
         }
     }
@@ -171,7 +171,7 @@ RT_DEV bool samplesSpeculate(const PassParams& P, unsigned int queued) {
 #ifndef RT_VOTE_MIN_CTAS
 #define RT_VOTE_MIN_CTAS 6
 #endif
-template <bool COUNT, bool IDS>
+template <bool COUNT, bool IDS, bool DEFER = false>
 __global__ void __launch_bounds__(kThreads, COUNT ? 1 : RT_VOTE_MIN_CTAS) rtVoteKernel(const __grid_constant__ PassParams P) {
     extern __shared__ uint2 smem[];
     if (P.specGate != 0 && samplesSpeculate(P, *P.queueCount)) return;    // the samples rounds did this pass
@@ -376,7 +376,7 @@ __global__ void __launch_bounds__(kThreads, COUNT ? 1 : RT_VOTE_MIN_CTAS) rtVote
             }
         } else if (__popc(mL) >= leafT || mI == 0u) {
             // ------------------------------------------------------------------- LEAF section
-            if (L.mode == MODE_LEAF) stepLeaf<COUNT>(sc, L, stack, stride, cnt);
+            if (L.mode == MODE_LEAF) stepLeaf<COUNT, DEFER>(sc, L, stack, stride, cnt);
         } else {
             // ------------------------------------------- INTERNAL section: a burst of node steps per vote
 #pragma unroll 1
