@@ -1,7 +1,7 @@
 // rt_spec.cuh — variant SAMPLES: the samples of a pixel-frame evaluated in parallel, bit-exactly.
 //
 // The reference carries the RNG state across the rays_per_pixel samples of a pixel-frame (fragment.glsl:358-363),
-// which chains them: a 64-spp pixel on the mesh is 128+ strictly sequential rays.  Measured on B200 (tools/
+// which chains them: a 64-spp pixel on the mesh is ~77 strictly sequential rays.  Measured on B200 (tools/
 // chain_probe.py): one 8x4 tile of the 4K/64-spp dragon frame takes 1.3-4.8 ms ALONE on an idle GPU, and 1/8 of the
 // frame takes 12.5 ms where the work is worth 3.5 ms — the chain, not the throughput, bounds a tile-sharded frame.
 //
