@@ -196,6 +196,25 @@ def _mode_worker(rank, world, port, out_dir):
     else:
         assert ctx.calls == ["render_pass(to_peer)"] * 2, ctx.calls
     peer.close()
+    # a mapping refused on ONE rank (ranks on different nodes, no peer access): every rank learns it, nobody keeps a
+    # half-open exchange, and the same frame then goes through the gather exchange
+    ctx = _OracleRenderer(oracle, tris, boxes, indices, cfg.width, cfg.height)
+    if rank == 1:
+        def refuse(handles):
+            raise RuntimeError("cudaIpcOpenMemHandle: invalid device context")
+        ctx.peer_open = refuse
+    assert distributed.open_peer_targets(ctx, dist, rank, world) is None
+    assert ctx.peer_image is None
+    distributed.render_tile_mode(ctx, dist, params, rank, world, frame=0, band_rows=4, peer=None)
+    if rank == 0:
+        np.save(os.path.join(out_dir, "tile_mode_fallback.npy"), np.asarray(ctx.image))
+    # unequal targets are a caller's error, reported on every rank before anything is mapped
+    ctx = _OracleRenderer(oracle, tris, boxes, indices, cfg.width, cfg.height + rank)
+    try:
+        distributed.open_peer_targets(ctx, dist, rank, world)
+        raise AssertionError("unequal targets accepted")
+    except RuntimeError as err:
+        assert "lockstep" in str(err)
     # frame mode in two instalments: frames 0..2, then 3..6 continued from rank 0's running mean
     ctx = _OracleRenderer(oracle, tris, boxes, indices, cfg.width, cfg.height)
     view = lambda c: torch.from_numpy(c.image)
@@ -220,6 +239,7 @@ def test_render_modes_through_the_public_functions(tmp_path, oracle_mod):
     params = cfg.params()
     single, _, _ = oracle_mod.render_pass(tris, boxes, indices, params)
     assert np.load(tmp_path / "tile_mode.npy").tobytes() == single.tobytes()
+    assert np.load(tmp_path / "tile_mode_fallback.npy").tobytes() == single.tobytes()
     two = oracle_mod.render_frames(tris, boxes, indices, params, 0, 2)
     assert np.load(tmp_path / "tile_mode_peer.npy").tobytes() == two.tobytes()
     mean = oracle_mod.render_frames(tris, boxes, indices, params, 0, 7)
