@@ -11,14 +11,16 @@ and reused by its 64 samples (they share it, fragment.glsl:361-362), so traced r
 rays — both are reported, the headline uses traced rays.
 
 N > 1: tile mode — rank g owns the interleaved 8-row bands (y // 8) % N == g of the SAME frame (strong
-scaling), the bands are gathered to rank 0 over NCCL inside the timed region.
+scaling).  The bands reach rank 0 inside the timed region: by default the render kernels of the other ranks store
+their pixels straight into rank 0's target over NVLink (CUDA IPC mapping, RT_PASS_TO_PEER; two 4-byte all-reduces as
+fences, "exchange": "peer"); --exchange gather packs them and uses an NCCL gather instead.
 
 JSON keys: "roofline" is the on-SM ceiling that binds the pass (L1 data-pipe wavefronts or warp issue, whichever
 fraction is larger; both kept as sub-objects; peaks micro-benchmarked on the same GPU right after the timed region,
 "measured_peaks"; counts per launch from the committed ncu capture, time live) — the scene is L2-resident by design, so
 the contract's algorithmic-bytes-per-second figure is reported as "algorithmic" without a fraction of the HBM
 peak, and "traffic" (DRAM bytes per launch) is the framebuffer.  "phases_ms": CUDA-event split of a step (flush+clear,
-pass, and for N > 1 pack / NCCL gather / scatter); "cpu_baseline"; "box_variant" (same frame size with the dragon inside
+pass, and for N > 1 the fence after the pass, or pack / NCCL gather / scatter); "cpu_baseline"; "box_variant" (same frame size with the dragon inside
 the reference's closed room: the realistic-throughput figure); "variant": what the library ran under AUTO.
 """
 from __future__ import annotations
